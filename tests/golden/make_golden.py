@@ -1,0 +1,246 @@
+#!/usr/bin/env python3
+"""Extract the reference's own literal test vectors for the hash-agg / hash-join path.
+
+Run in the build container (needs /root/reference, which does NOT exist on the GPU box):
+
+    python tests/golden/make_golden.py
+
+It parses the Rust test sources / sqllogictest files of the reference and writes
+``tests/golden/hash_join.json`` and ``tests/golden/aggregates.json``.  Inputs and expected
+outputs are taken verbatim from the cited line ranges; nothing is computed here, so the JSON is a
+transcription of the reference's known-answer tests that travels with the repo.
+"""
+import csv
+import json
+import os
+import re
+import sys
+
+REF = os.environ.get("DF_REFERENCE", "/root/reference")
+HERE = os.path.dirname(os.path.abspath(__file__))
+HJ = "datafusion/physical-plan/src/joins/hash_join.rs"
+AGG = "datafusion/physical-plan/src/aggregates/mod.rs"
+
+
+def read(rel):
+    with open(os.path.join(REF, rel)) as f:
+        return f.read().split("\n")
+
+
+def parse_table(lines):
+    """Parse an arrow pretty-printed table given as Rust string literals."""
+    rows = [re.search(r'"(.*)"', l).group(1) for l in lines if '"' in l]
+    rows = [r for r in rows if r.startswith("|")]
+    cells = [[c.strip() for c in r.strip("|").split("|")] for r in rows]
+    header, body = cells[0], cells[1:]
+    return header, [[None if c == "" else c for c in r] for r in body]
+
+
+def find_fn(lines, name):
+    pat = re.compile(r"\bfn %s\b" % re.escape(name))
+    start = next(i for i, l in enumerate(lines) if pat.search(l))
+    depth, seen, i = 0, False, start
+    while True:
+        depth += lines[i].count("{") - lines[i].count("}")
+        seen = seen or "{" in lines[i]
+        if seen and depth == 0:
+            return start, i
+        i += 1
+
+
+TABLE_RE = re.compile(r'\(\s*"(\w+)",\s*&vec!\[([^\]]*)\]\s*\)', re.S)
+
+
+def parse_build_tables(text):
+    """All build_table*(...) calls in order: [(kind, [(name, [ints])...])]."""
+    out = []
+    for m in re.finditer(r"(build_table_two_batches|build_table_i32|build_table)\(", text):
+        depth, j = 1, m.end()
+        while depth:
+            depth += {"(": 1, ")": -1}.get(text[j], 0)
+            j += 1
+        body = text[m.end():j - 1]
+        cols = [(n, [int(x) for x in v.replace("\n", " ").split(",") if x.strip()]) for n, v in TABLE_RE.findall(body)]
+        if cols:
+            out.append((m.group(1), cols))
+    return out
+
+
+def join_cases():
+    lines = read(HJ)
+    src = "\n".join(lines)
+    helpers = {}
+    for h in ("build_semi_anti_left_table", "build_semi_anti_right_table"):
+        s, e = find_fn(lines, h)
+        helpers[h] = parse_build_tables("\n".join(lines[s:e + 1]))[0]
+    names = [
+        "join_inner_one", "partitioned_join_inner_one", "join_inner_one_no_shared_column_names",
+        "join_inner_one_randomly_ordered", "join_inner_two", "join_left_multi_batch", "join_full_multi_batch",
+        "join_left_empty_right", "join_full_empty_right", "join_left_one", "partitioned_join_left_one",
+        "join_left_semi", "join_right_semi", "join_left_anti", "join_right_anti", "join_right_one",
+        "partitioned_join_right_one", "join_full_one",
+    ]
+    cases = []
+    for name in names:
+        s, e = find_fn(lines, name)
+        body = "\n".join(lines[s:e + 1])
+        tables = parse_build_tables(body)
+        sides = {}
+        for side in ("left", "right"):
+            m = re.search(r"let %s = (build_\w+)\(" % side, body)
+            if m.group(1) in helpers:
+                sides[side] = helpers[m.group(1)]
+            else:
+                sides[side] = tables.pop(0)
+        on = re.findall(r'Column::new_with_schema\("(\w+)", &(left|right)\.schema\(\)', body)
+        pairs = [(on[i][0], on[i + 1][0]) for i in range(0, len(on), 2)]
+        jt = re.search(r"&JoinType::(\w+)", body).group(1)
+        es = next(i for i in range(s, e) if "let expected = [" in lines[i])
+        ee = next(i for i in range(es, e) if lines[i].strip() == "];")
+        header, rows = parse_table(lines[es:ee + 1])
+        ordered = "assert_batches_eq!(expected" in body
+        def side_json(t):
+            kind, cols = t
+            batch = {"names": [c[0] for c in cols], "columns": [c[1] for c in cols]}
+            return {"batches": [batch, batch] if kind == "build_table_two_batches" else [batch]}
+        cases.append({
+            "name": name, "source": "%s:%d-%d" % (HJ, s + 1, e + 1), "join_type": jt,
+            "left": side_json(sides["left"]), "right": side_json(sides["right"]),
+            "on": pairs, "expected_header": header,
+            "expected": [[None if c is None else int(c) for c in r] for r in rows],
+            "ordered": ordered,
+        })
+    # join_inner_one_two_parts_left: two build batches (hash_join.rs:1780-1837)
+    s, e = find_fn(lines, "join_inner_one_two_parts_left")
+    body = "\n".join(lines[s:e + 1])
+    t = parse_build_tables(body)
+    es = next(i for i in range(s, e) if "let expected = [" in lines[i])
+    ee = next(i for i in range(es, e) if lines[i].strip() == "];")
+    header, rows = parse_table(lines[es:ee + 1])
+    mk = lambda cols: {"names": [c[0] for c in cols], "columns": [c[1] for c in cols]}
+    cases.append({
+        "name": "join_inner_one_two_parts_left", "source": "%s:%d-%d" % (HJ, s + 1, e + 1), "join_type": "Inner",
+        "left": {"batches": [mk(t[0][1]), mk(t[1][1])]}, "right": {"batches": [mk(t[2][1])]},
+        "on": [("a1", "a1"), ("b2", "b2")], "expected_header": header,
+        "expected": [[None if c is None else int(c) for c in r] for r in rows],
+        # collected through CoalescePartitionsExec over two partitions: arrival order of the two
+        # build batches is not fixed, so compare sorted.
+        "ordered": False,
+    })
+    # join_with_hash_collision (hash_join.rs:2883-2943): every key collides; lookup must return (0,0),(1,1)
+    s, e = find_fn(lines, "join_with_hash_collision")
+    t = parse_build_tables("\n".join(lines[s:e + 1]))
+    cases.append({
+        "name": "join_with_hash_collision", "source": "%s:%d-%d" % (HJ, s + 1, e + 1), "join_type": "Inner",
+        "left": {"batches": [mk(t[0][1])]}, "right": {"batches": [mk(t[1][1])]}, "on": [("a", "a")],
+        "force_collisions": True, "expected_header": ["a", "x", "y", "a", "b", "c"],
+        "expected": [[10, 100, 200, 10, 0, 30], [20, 200, 300, 20, 0, 40]], "ordered": True,
+    })
+    return cases
+
+
+def agg_cases():
+    lines = read(AGG)
+    out = {}
+    # some_data() (aggregates/mod.rs:1256-1285)
+    s, e = find_fn(lines, "some_data")
+    body = "\n".join(lines[s:e + 1])
+    a = [[int(x) for x in m.split(",")] for m in re.findall(r"UInt32Array::from\(vec!\[([^\]]*)\]", body)]
+    b = [[float(x) for x in m.split(",")] for m in re.findall(r"Float64Array::from\(vec!\[([^\]]*)\]", body)]
+    out["some_data"] = {"source": "%s:%d-%d" % (AGG, s + 1, e + 1),
+                        "batches": [{"a": a[i], "b": b[i]} for i in range(len(a))]}
+    # check_aggregates (mod.rs:1509-1615): Partial state then Final AVG
+    s, e = find_fn(lines, "check_aggregates")
+    tabs = []
+    i = s
+    while i < e:
+        if re.search(r"let expected = (if spill \{|vec!\[|\[)", lines[i]) or lines[i].strip() in ("vec![", "[") and False:
+            pass
+        i += 1
+    # collect every literal table in the function, in order
+    blocks, cur = [], None
+    for i in range(s, e + 1):
+        l = lines[i].strip()
+        if l.startswith('"+') or l.startswith('"|'):
+            if cur is None:
+                cur = [i, i]
+            cur[1] = i
+        elif cur is not None:
+            blocks.append(tuple(cur))
+            cur = None
+    tables = [parse_table(lines[b0:b1 + 1]) + ((b0 + 1, b1 + 1),) for b0, b1 in blocks]
+    # order in source: partial(spill), partial(no spill), final
+    out["check_aggregates"] = {
+        "source": "%s:%d-%d" % (AGG, s + 1, e + 1),
+        "partial_no_spill": {"header": tables[1][0], "rows": tables[1][1], "lines": tables[1][2]},
+        "final": {"header": tables[2][0], "rows": tables[2][1], "lines": tables[2][2]},
+    }
+    # check_grouping_sets (mod.rs:1353-1506)
+    s, e = find_fn(lines, "check_grouping_sets")
+    blocks, cur = [], None
+    for i in range(s, e + 1):
+        l = lines[i].strip()
+        if l.startswith('"+') or l.startswith('"|'):
+            if cur is None:
+                cur = [i, i]
+            cur[1] = i
+        elif cur is not None:
+            blocks.append(tuple(cur))
+            cur = None
+    tables = [parse_table(lines[b0:b1 + 1]) + ((b0 + 1, b1 + 1),) for b0, b1 in blocks]
+    out["check_grouping_sets"] = {
+        "source": "%s:%d-%d" % (AGG, s + 1, e + 1),
+        "groups": [[False, True], [True, False], [False, False]],
+        "partial_no_spill": {"header": tables[1][0], "rows": tables[1][1], "lines": tables[1][2]},
+        "final": {"header": tables[2][0], "rows": tables[2][1], "lines": tables[2][2]},
+    }
+    # avg_decimal family (physical-expr/src/aggregate/average.rs:570-640)
+    avg = read("datafusion/physical-expr/src/aggregate/average.rs")
+    s, e = find_fn(avg, "avg_decimal")
+    body = "\n".join(avg[s:e + 1])
+    m = re.search(r"ScalarValue::Decimal128\(Some\((\d+)\), (\d+), (\d+)\)", body)
+    out["avg_decimal"] = {"source": "datafusion/physical-expr/src/aggregate/average.rs:%d-%d" % (s + 1, e + 1),
+                          "input": list(range(1, 7)), "input_type": [10, 0],
+                          "expected_unscaled": int(m.group(1)), "expected_type": [int(m.group(2)), int(m.group(3))]}
+    s, e = find_fn(avg, "avg_decimal_with_nulls")
+    body = "\n".join(avg[s:e + 1])
+    m = re.search(r"ScalarValue::Decimal128\(Some\((\d+)\), (\d+), (\d+)\)", body)
+    out["avg_decimal_with_nulls"] = {
+        "source": "datafusion/physical-expr/src/aggregate/average.rs:%d-%d" % (s + 1, e + 1),
+        "input": [None if i == 2 else i for i in range(1, 6)], "input_type": [10, 0],
+        "expected_unscaled": int(m.group(1)), "expected_type": [int(m.group(2)), int(m.group(3))]}
+    # decimal.slt goldens over core/tests/data/decimal_data.csv
+    with open(os.path.join(REF, "datafusion/core/tests/data/decimal_data.csv")) as f:
+        rows = list(csv.DictReader(f))
+    slt = read("datafusion/sqllogictest/test_files/decimal.slt")
+    def after(query):
+        i = next(k for k, l in enumerate(slt) if l.strip() == query)
+        j = i + 2
+        res = []
+        while slt[j].strip():
+            res.append(slt[j].split())
+            j += 1
+        return res, "datafusion/sqllogictest/test_files/decimal.slt:%d-%d" % (i + 1, j)
+    d = {"csv": "datafusion/core/tests/data/decimal_data.csv", "c1": [r["c1"] for r in rows],
+         "c4": [r["c4"] == "true" for r in rows], "c1_type": [10, 6]}
+    d["sum_c1"], d["sum_c1_src"] = after("select arrow_typeof(sum(c1)), sum(c1) from decimal_simple;")
+    d["avg_c1"], d["avg_c1_src"] = after("select arrow_typeof(avg(c1)), avg(c1) from decimal_simple;")
+    d["count_by_c1"], d["count_by_c1_src"] = after("select count(*),c1 from decimal_simple group by c1 order by c1;")
+    d["count_by_c1_c4"], d["count_by_c1_c4_src"] = after(
+        "select count(*),c1,c4 from decimal_simple group by c1,c4 order by c1,c4;")
+    out["decimal_slt"] = d
+    return out
+
+
+def main():
+    if not os.path.isdir(REF):
+        sys.exit("reference tree not found at %s (goldens are pre-generated; nothing to do)" % REF)
+    with open(os.path.join(HERE, "hash_join.json"), "w") as f:
+        json.dump(join_cases(), f, indent=1)
+    with open(os.path.join(HERE, "aggregates.json"), "w") as f:
+        json.dump(agg_cases(), f, indent=1)
+    print("wrote hash_join.json, aggregates.json")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,178 @@
+"""Pins the CPU oracle to the reference's own literal test vectors (tests/golden/*.json, generated
+from the reference sources by tests/golden/make_golden.py).  CPU-only."""
+import decimal
+import json
+import os
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+import oracle
+from oracle import AggSpec, OracleAgg
+from util import assert_rows_equal, rows_of
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+JOINS = json.load(open(os.path.join(G, "hash_join.json")))
+AGGS = json.load(open(os.path.join(G, "aggregates.json")))
+JT = {"Inner": "inner", "Left": "left", "Right": "right", "Full": "full", "LeftSemi": "left_semi",
+      "RightSemi": "right_semi", "LeftAnti": "left_anti", "RightAnti": "right_anti"}
+
+
+def batches(side):
+    out = []
+    for b in side["batches"]:
+        out.append(pa.record_batch([pa.array(c, pa.int32()) for c in b["columns"]], names=b["names"]))
+    return out
+
+
+# the reference runs every join test with these batch sizes (hash_join.rs:1434)
+@pytest.mark.parametrize("batch_size", [8192, 10, 5, 2, 1])
+@pytest.mark.parametrize("case", JOINS, ids=[c["name"] for c in JOINS])
+def test_join_golden(case, batch_size):
+    left, right = batches(case["left"]), batches(case["right"])
+    on = [(left[0].schema.names.index(l), right[0].schema.names.index(r)) for l, r in case["on"]]
+    t = oracle.hash_join(JT[case["join_type"]], left, right, on, batch_size=batch_size,
+                         force_collisions=case.get("force_collisions", False))
+    assert t.schema.names == case["expected_header"]
+    want = [tuple(r) for r in case["expected"]]
+    assert_rows_equal(rows_of(t), want, ordered=case["ordered"], what=case["name"])
+
+
+def test_join_inner_two_batch_count():
+    # hash_join.rs:1752-1758: ceil(3 / batch_size) output batches, +1 empty batch when batch_size == 1
+    case = next(c for c in JOINS if c["name"] == "join_inner_two")
+    left, right = batches(case["left"]), batches(case["right"])
+    for bs in (8192, 10, 5, 2, 1):
+        oracle.hash_join("inner", left, right, [(0, 0), (1, 1)], batch_size=bs)
+        expect = -(-3 // bs) + (1 if bs == 1 else 0)
+        assert oracle.hash_join.last_out_batches == expect
+
+
+def some_data():
+    return [pa.record_batch([pa.array(b["a"], pa.uint32()), pa.array(b["b"], pa.float64())], names=["a", "b"])
+            for b in AGGS["some_data"]["batches"]]
+
+
+def test_check_aggregates():
+    g = AGGS["check_aggregates"]
+    aggs = [AggSpec("avg", "AVG(b)", pa.float64())]
+    p = OracleAgg("partial", ["a"], [pa.uint32()], aggs)
+    for b in some_data():
+        p.push([b.column(0)], [b.column(1)])
+    st = p.emit()
+    assert st.schema.names == g["partial_no_spill"]["header"]
+    want = [(int(a), int(c), float(s)) for a, c, s in g["partial_no_spill"]["rows"]]
+    assert_rows_equal(rows_of(st), want)
+    f = OracleAgg("final", ["a"], [pa.uint32()], aggs)
+    f.push([st.column(0)], [st.column(1), st.column(2)])
+    out = f.emit()
+    assert out.schema.names == g["final"]["header"]
+    want = [(int(a), float(v)) for a, v in g["final"]["rows"]]
+    assert_rows_equal(rows_of(out), want, rel=0.0)   # bit-exact: 2.3333333333333335, 3.6666666666666665
+
+
+def test_check_grouping_sets():
+    # one intern+update pass per grouping set with NULL-substituted key columns (aggregates/mod.rs:1183-1199)
+    g = AGGS["check_grouping_sets"]
+    aggs = [AggSpec("count", "COUNT(1)", None)]
+    p = OracleAgg("partial", ["a", "b"], [pa.uint32(), pa.float64()], aggs)
+    for b in some_data():
+        for null_a, null_b in g["groups"]:
+            a = pa.nulls(b.num_rows, pa.uint32()) if null_a else b.column(0)
+            bb = pa.nulls(b.num_rows, pa.float64()) if null_b else b.column(1)
+            p.push([a, bb], [None])
+    st = p.emit()
+    conv = lambda r: (None if r[0] is None else int(r[0]), None if r[1] is None else float(r[1]), int(r[2]))
+    assert_rows_equal(rows_of(st), [conv(r) for r in g["partial_no_spill"]["rows"]])
+    f = OracleAgg("final", ["a", "b"], [pa.uint32(), pa.float64()], aggs)
+    f.push([st.column(0), st.column(1)], [st.column(2)])
+    assert_rows_equal(rows_of(f.emit()), [conv(r) for r in g["final"]["rows"]])
+
+
+@pytest.mark.parametrize("name", ["avg_decimal", "avg_decimal_with_nulls"])
+def test_avg_decimal(name):
+    g = AGGS[name]
+    t = pa.decimal128(*g["input_type"])
+    arr = pa.array([None if v is None else decimal.Decimal(v) for v in g["input"]], t)
+    a = OracleAgg("single", ["k"], [pa.int8()], [AggSpec("avg", "avg", t)])
+    a.push([pa.array([0] * len(arr), pa.int8())], [arr])
+    out = a.emit()
+    assert out.schema.field(1).type == pa.decimal128(*g["expected_type"])
+    got = out.column(1)[0].as_py()
+    assert got == decimal.Decimal(g["expected_unscaled"]).scaleb(-g["expected_type"][1])
+
+
+def test_avg_decimal_all_nulls():
+    t = pa.decimal128(10, 0)
+    a = OracleAgg("single", ["k"], [pa.int8()], [AggSpec("avg", "avg", t)])
+    a.push([pa.array([0] * 6, pa.int8())], [pa.nulls(6, t)])
+    assert a.emit().column(1).to_pylist() == [None]     # average.rs:613-629
+
+
+def test_decimal_slt():
+    d = AGGS["decimal_slt"]
+    t = pa.decimal128(*d["c1_type"])
+    c1 = pa.array([decimal.Decimal(v) for v in d["c1"]], t)
+    c4 = pa.array(d["c4"], pa.bool_())
+    one = pa.array([0] * len(c1), pa.int8())
+    a = OracleAgg("single", ["k"], [pa.int8()], [AggSpec("sum", "s", t), AggSpec("avg", "a", t)])
+    a.push([one], [c1, c1])
+    out = a.emit()
+    # decimal.slt:112-124 — Decimal128(20,6) 0.00055 ; Decimal128(14,10) 0.0000366666 (truncation)
+    assert out.schema.field(1).type == pa.decimal128(20, 6)
+    assert out.schema.field(2).type == pa.decimal128(14, 10)
+    assert out.column(1)[0].as_py() == decimal.Decimal(d["sum_c1"][0][-1])
+    assert out.column(2)[0].as_py() == decimal.Decimal(d["avg_c1"][0][-1])
+    a = OracleAgg("single", ["c1"], [t], [AggSpec("count", "c", None)])
+    a.push([c1], [None])
+    want = [(decimal.Decimal(v), int(c)) for c, v in d["count_by_c1"]]
+    assert_rows_equal(rows_of(a.emit()), want)
+    a = OracleAgg("single", ["c1", "c4"], [t, pa.bool_()], [AggSpec("count", "c", None)])
+    a.push([c1, c4], [None])
+    want = [(decimal.Decimal(v), b == "true", int(c)) for c, v, b in d["count_by_c1_c4"]]
+    assert_rows_equal(rows_of(a.emit()), want)
+
+
+def test_hash_properties():
+    # the reference asserts only properties of create_hashes (hash_utils.rs:450-728)
+    s = pa.array(["foo", None, "bar", "foo", "", None])
+    h = oracle.create_hashes([s])
+    assert h[0] == h[3] and h[1] == 0 and h[5] == 0 and h[0] != h[2] and h[4] != 0
+    hd = oracle.create_hashes([s.dictionary_encode()])
+    assert (h == hd).all()                                   # dict hashes == plain hashes (:520-562)
+    i = pa.array([1, 2, None, 1], pa.int64())
+    h2 = oracle.create_hashes([s.slice(0, 4), i])
+    h2d = oracle.create_hashes([s.slice(0, 4).dictionary_encode(), i])
+    assert (h2 == h2d).all() and h2[0] == h2[3] and h2[0] != h2[1]
+    f = pa.array([0.0, -0.0, float("nan"), float("nan")])
+    hf = oracle.create_hashes([f])
+    assert hf[0] != hf[1] and hf[2] == hf[3]                 # bit-pattern hashing (:78-87)
+    assert (oracle.create_hashes([i], force_collisions=True) == 0).all()
+
+
+def test_partition_conserves_rows():
+    rng = np.random.default_rng(0)
+    b = pa.record_batch([pa.array(rng.integers(0, 50, 1000)), pa.array(rng.random(1000))], names=["k", "v"])
+    parts = oracle.partition(b, [0], 7)
+    assert sum(p.num_rows for p in parts if p is not None) == 1000   # repartition/mod.rs:1010-1031
+    seen = {}
+    for pi, p in enumerate(parts):
+        if p is None:
+            continue
+        for k in p.column(0).to_pylist():
+            assert seen.setdefault(k, pi) == pi
+
+
+def test_emit_first_n_and_float_minmax_quirks():
+    a = OracleAgg("single", ["k"], [pa.int64()], [AggSpec("max", "mx", pa.float64()), AggSpec("min", "mn", pa.float64()),
+                                                   AggSpec("count", "c", pa.float64())])
+    k = pa.array([1, 1, 2, 3, 3, 4], pa.int64())
+    v = pa.array([float("nan"), float("nan"), float("-inf"), 1.5, None, None], pa.float64())
+    a.push([k], [v, v, v])
+    first = a.emit(2)
+    rest = a.emit()
+    import sys
+    # min_max.rs:102-139: NaN never replaces the start value; start values are finite f64::MIN/MAX
+    assert rows_of(first) == [(1, -sys.float_info.max, sys.float_info.max, 2), (2, -sys.float_info.max, float("-inf"), 1)]
+    assert rows_of(rest) == [(3, 1.5, 1.5, 1), (4, None, None, 0)]
