@@ -1,0 +1,1088 @@
+// batch.cu — context, memory, Arrow C Data import/export and the columnar utility kernels
+// (take / concat / slice / bitmap realign / prefix sum) that stand in for arrow-rs
+// `compute::{take, concat_batches}` on the device (joins/utils.rs:1180-1230, hash_join.rs:764).
+#include <algorithm>
+
+#include "common.h"
+#include "device.cuh"
+
+namespace dfgpu {
+
+// ------------------------------------------------------------------------------------------------
+// errors / types
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+void set_last_error(const std::string &m) { g_last_error = m; }
+const std::string &last_error() { return g_last_error; }
+
+int type_width(int32_t id) {
+    switch (id) {
+    case T_I8: case T_U8: return 1;
+    case T_I16: case T_U16: return 2;
+    case T_I32: case T_U32: case T_F32: case T_DATE32: case T_TIME32: return 4;
+    case T_I64: case T_U64: case T_F64: case T_DATE64: case T_TS: case T_TIME64: return 8;
+    case T_DEC128: return 16;
+    default: return 0;
+    }
+}
+int TypeInfo::width() const { return type_width(id); }
+std::string TypeInfo::describe() const {
+    if (id == T_DICT) return "Dictionary(" + std::to_string(index_id) + "," + value->describe() + ")";
+    return format.empty() ? format_of(*this) : format;
+}
+
+std::string format_of(const TypeInfo &t) {
+    if (!t.format.empty()) return t.format;
+    switch (t.id) {
+    case T_BOOL: return "b";
+    case T_I8: return "c";
+    case T_U8: return "C";
+    case T_I16: return "s";
+    case T_U16: return "S";
+    case T_I32: return "i";
+    case T_U32: return "I";
+    case T_I64: return "l";
+    case T_U64: return "L";
+    case T_F32: return "f";
+    case T_F64: return "g";
+    case T_DATE32: return "tdD";
+    case T_DATE64: return "tdm";
+    case T_TS: return "tsu:";
+    case T_TIME32: return "ttm";
+    case T_TIME64: return "ttu";
+    case T_DEC128: return "d:" + std::to_string(t.precision) + "," + std::to_string(t.scale);
+    case T_UTF8: return "u";
+    case T_LARGE_UTF8: return "U";
+    case T_BINARY: return "z";
+    case T_LARGE_BINARY: return "Z";
+    }
+    fail(DFGPU_INTERNAL, "format_of: unknown type");
+}
+
+static int32_t id_from_format(const std::string &f, int &prec, int &scale) {
+    if (f == "b") return T_BOOL;
+    if (f == "c") return T_I8;
+    if (f == "C") return T_U8;
+    if (f == "s") return T_I16;
+    if (f == "S") return T_U16;
+    if (f == "i") return T_I32;
+    if (f == "I") return T_U32;
+    if (f == "l") return T_I64;
+    if (f == "L") return T_U64;
+    if (f == "f") return T_F32;
+    if (f == "g") return T_F64;
+    if (f == "u") return T_UTF8;
+    if (f == "U") return T_LARGE_UTF8;
+    if (f == "z") return T_BINARY;
+    if (f == "Z") return T_LARGE_BINARY;
+    if (f == "tdD") return T_DATE32;
+    if (f == "tdm") return T_DATE64;
+    if (f == "tts" || f == "ttm") return T_TIME32;
+    if (f == "ttu" || f == "ttn") return T_TIME64;
+    if (f.rfind("ts", 0) == 0 || f.rfind("tD", 0) == 0) return T_TS;  // timestamps / durations: int64
+    if (f.rfind("d:", 0) == 0) {
+        int bits = 128;
+        int n = sscanf(f.c_str(), "d:%d,%d,%d", &prec, &scale, &bits);
+        if (n < 2) fail(DFGPU_NOT_IMPLEMENTED, "bad decimal format " + f);
+        if (bits != 128) fail(DFGPU_NOT_IMPLEMENTED, "This feature is not implemented: Decimal" + std::to_string(bits));
+        return T_DEC128;
+    }
+    fail(DFGPU_NOT_IMPLEMENTED, "This feature is not implemented: Arrow type with format '" + f + "'");
+}
+
+TypeInfo type_from_schema(const ArrowSchema *s) {
+    TypeInfo t;
+    t.name = s->name ? s->name : "";
+    t.nullable = (s->flags & ARROW_FLAG_NULLABLE) != 0;
+    std::string f = s->format;
+    int p = 0, sc = 0;
+    int32_t id = id_from_format(f, p, sc);
+    if (s->dictionary) {
+        t.id = T_DICT;
+        t.index_id = id;
+        t.dict_ordered = (s->flags & ARROW_FLAG_DICTIONARY_ORDERED) != 0;
+        t.value = std::make_shared<TypeInfo>(type_from_schema(s->dictionary));
+        t.format = f;  // index format
+        return t;
+    }
+    t.id = id;
+    t.precision = p;
+    t.scale = sc;
+    t.format = f;
+    return t;
+}
+TypeInfo make_type(int32_t id, const std::string &name, bool nullable, int precision, int scale) {
+    TypeInfo t;
+    t.id = id; t.name = name; t.nullable = nullable; t.precision = precision; t.scale = scale;
+    t.format = format_of(t);
+    return t;
+}
+Schema schema_from_arrow(const ArrowSchema *s) {
+    if (!s || !s->format || std::string(s->format) != "+s")
+        fail(DFGPU_PLAN, "expected a struct schema ('+s') describing a RecordBatch");
+    Schema out;
+    for (int64_t i = 0; i < s->n_children; i++) out.fields.push_back(type_from_schema(s->children[i]));
+    return out;
+}
+
+// ---- schema export -----------------------------------------------------------------------------
+struct SchemaPriv {
+    std::string format, name;
+    std::vector<ArrowSchema> child_store;
+    std::vector<ArrowSchema *> child_ptrs;
+    ArrowSchema dict;
+    bool has_dict = false;
+};
+static void release_schema(ArrowSchema *s) {
+    if (!s || !s->release) return;
+    auto *p = (SchemaPriv *)s->private_data;
+    for (auto &c : p->child_store)
+        if (c.release) c.release(&c);
+    if (p->has_dict && p->dict.release) p->dict.release(&p->dict);
+    delete p;
+    s->release = nullptr;
+}
+static void field_to_arrow(const TypeInfo &t, ArrowSchema *out) {
+    auto *p = new SchemaPriv();
+    memset(out, 0, sizeof *out);
+    p->name = t.name;
+    if (t.id == T_DICT) {
+        TypeInfo idx;
+        idx.id = t.index_id;
+        p->format = t.format.empty() ? format_of(idx) : t.format;
+        p->has_dict = true;
+        field_to_arrow(*t.value, &p->dict);
+        out->dictionary = &p->dict;
+        if (t.dict_ordered) out->flags |= ARROW_FLAG_DICTIONARY_ORDERED;
+    } else {
+        p->format = format_of(t);
+    }
+    out->format = p->format.c_str();
+    out->name = p->name.c_str();
+    if (t.nullable) out->flags |= ARROW_FLAG_NULLABLE;
+    out->release = release_schema;
+    out->private_data = p;
+}
+void schema_to_arrow(const Schema &s, ArrowSchema *out) {
+    auto *p = new SchemaPriv();
+    memset(out, 0, sizeof *out);
+    p->format = "+s";
+    p->child_store.resize(s.fields.size());
+    for (size_t i = 0; i < s.fields.size(); i++) {
+        field_to_arrow(s.fields[i], &p->child_store[i]);
+        p->child_ptrs.push_back(&p->child_store[i]);
+    }
+    out->format = p->format.c_str();
+    out->name = p->name.c_str();
+    out->n_children = (int64_t)s.fields.size();
+    out->children = p->child_ptrs.data();
+    out->release = release_schema;
+    out->private_data = p;
+}
+
+// ------------------------------------------------------------------------------------------------
+// memory
+// ------------------------------------------------------------------------------------------------
+static PinnedPool &pinned_pool() {
+    static PinnedPool *p = new PinnedPool();  // intentionally leaked: exported arrays may outlive any ctx
+    return *p;
+}
+void *PinnedPool::alloc(size_t bytes) {
+    size_t sz = 4096;
+    while (sz < bytes) sz <<= 1;
+    {
+        std::lock_guard<std::mutex> g(mu);
+        auto it = free_list.find(sz);
+        if (it != free_list.end()) {
+            void *p = it->second;
+            free_list.erase(it);
+            cached -= sz;
+            return p;
+        }
+    }
+    void *p = nullptr;
+    cudaError_t e = cudaMallocHost(&p, sz);
+    if (e != cudaSuccess) {
+        trim();
+        e = cudaMallocHost(&p, sz);
+        if (e != cudaSuccess) fail(DFGPU_RESOURCES_EXHAUSTED, std::string("pinned host allocation failed: ") + cudaGetErrorString(e));
+    }
+    std::lock_guard<std::mutex> g(mu);
+    sizes[p] = sz;
+    return p;
+}
+void PinnedPool::release(void *p) {
+    if (!p) return;
+    std::lock_guard<std::mutex> g(mu);
+    size_t sz = sizes[p];
+    if (cached + sz > (size_t)16 << 30) {
+        sizes.erase(p);
+        cudaFreeHost(p);
+        return;
+    }
+    free_list.emplace(sz, p);
+    cached += sz;
+}
+void PinnedPool::trim() {
+    std::lock_guard<std::mutex> g(mu);
+    for (auto &kv : free_list) {
+        sizes.erase(kv.second);
+        cudaFreeHost(kv.second);
+    }
+    free_list.clear();
+    cached = 0;
+}
+void *pinned_alloc(size_t n) { return pinned_pool().alloc(n); }
+void pinned_free(void *p) { pinned_pool().release(p); }
+
+DevBuf::DevBuf(Ctx *c, size_t n, bool zero) : ctx(c), bytes(n) {
+    if (n == 0) return;
+    cudaError_t e = cudaMallocAsync(&ptr, n, c->stream);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        // ResourcesExhausted, like MemoryReservation::try_grow failing (hash_join.rs:708,738)
+        fail(DFGPU_RESOURCES_EXHAUSTED, "Resources exhausted: failed to allocate " + std::to_string(n) +
+                                            " bytes of device memory: " + cudaGetErrorString(e));
+    }
+    if (zero) DF_CUDA(cudaMemsetAsync(ptr, 0, n, c->stream));
+}
+DevBuf::~DevBuf() {
+    if (ptr) cudaFreeAsync(ptr, ctx->stream);
+}
+
+ColView DevCol::view() const {
+    ColView v;
+    v.validity = validity;
+    v.values = values;
+    v.offsets = offsets;
+    v.vbit = vbit;
+    v.dbit = dbit;
+    v.type = type.id;
+    v.width = type.id == T_DICT ? type_width(type.index_id) : type.width();
+    v.large = type.is_large() ? 1 : 0;
+    TypeInfo it;
+    it.id = type.index_id;
+    v.index_signed = type.id == T_DICT ? (it.is_signed_int() ? 1 : 0) : 0;
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// small kernels
+// ------------------------------------------------------------------------------------------------
+// dst bit i = src bit (sbit + i), i < n; dst is word-aligned, tail bits zero
+__global__ void k_bitmap_realign(uint32_t *dst, const uint8_t *src, int64_t sbit, int64_t n) {
+    int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int64_t nw = (n + 31) / 32;
+    for (; w < nw; w += (int64_t)gridDim.x * blockDim.x) {
+        int64_t b0 = sbit + 32 * w;
+        int64_t byte = b0 >> 3;
+        int sh = (int)(b0 & 7);
+        int64_t last_byte = (sbit + n - 1) >> 3;
+        uint64_t acc = 0;
+        for (int k = 0; k < 5; k++)
+            if (byte + k <= last_byte) acc |= (uint64_t)src[byte + k] << (8 * k);
+        uint32_t v = (uint32_t)(acc >> sh);
+        int64_t rem = n - 32 * w;
+        if (rem < 32) v &= (rem <= 0) ? 0u : ((1u << rem) - 1u);
+        dst[w] = v;
+    }
+}
+// dst bit (dbit + i) = src bit (sbit + i) for i < n; dst pre-zeroed, concurrent writers use atomicOr
+__global__ void k_bitmap_append(uint32_t *dst, int64_t dbit, const uint8_t *src, int64_t sbit, int64_t n, int all_valid) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        bool v = all_valid ? true : bit_get(src, sbit + i);
+        if (v) atomicOr(&dst[(dbit + i) >> 5], 1u << ((dbit + i) & 31));
+    }
+}
+__global__ void k_count_unset(const uint8_t *bm, int64_t sbit, int64_t n, unsigned long long *out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    unsigned long long c = 0;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) c += bit_get(bm, sbit + i) ? 0 : 1;
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+__global__ void k_rebase_offsets32(int32_t *dst, const int32_t *src, int64_t n1, int64_t base, int64_t add) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n1; i += (int64_t)gridDim.x * blockDim.x) dst[i] = (int32_t)((int64_t)src[i] - base + add);
+}
+__global__ void k_rebase_offsets64(int64_t *dst, const int64_t *src, int64_t n1, int64_t base, int64_t add) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n1; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i] - base + add;
+}
+__global__ void k_iota(void *dst, int width, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        switch (width) {
+        case 1: ((uint8_t *)dst)[i] = (uint8_t)i; break;
+        case 2: ((uint16_t *)dst)[i] = (uint16_t)i; break;
+        case 4: ((uint32_t *)dst)[i] = (uint32_t)i; break;
+        default: ((uint64_t *)dst)[i] = (uint64_t)i; break;
+        }
+    }
+}
+
+int64_t count_nulls(Ctx *ctx, const uint8_t *validity, int64_t vbit, int64_t n) {
+    if (!validity || n == 0) return 0;
+    DevBuf cnt(ctx, 8, true);
+    k_count_unset<<<grid_for(n, 256, ctx, 8), 256, 0, ctx->stream>>>(validity, vbit, n, cnt.as<unsigned long long>());
+    note_launch(ctx);
+    unsigned long long h = 0;
+    DF_CUDA(cudaMemcpyAsync(&h, cnt.ptr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    DF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return (int64_t)h;
+}
+
+// ---- exclusive prefix sum: block scan -> recursive scan of block totals -> add back -------------
+static const int SCAN_BLOCK = 256, SCAN_ITEMS = 8, SCAN_TILE = SCAN_BLOCK * SCAN_ITEMS;
+__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_tiles(const int64_t *in, int64_t *out, int64_t n, int64_t *tile_sums) {
+    __shared__ int64_t warp_sums[SCAN_BLOCK / 32];
+    int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    int64_t v[SCAN_ITEMS];
+    int64_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        v[k] = (base + k < n) ? in[base + k] : 0;
+        sum += v[k];
+    }
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int64_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int64_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int64_t w = lane < SCAN_BLOCK / 32 ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int64_t t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        if (lane < SCAN_BLOCK / 32) warp_sums[lane] = w;
+    }
+    __syncthreads();
+    int64_t excl = incl - sum + (wid ? warp_sums[wid - 1] : 0);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        if (base + k < n) out[base + k] = excl;
+        excl += v[k];
+    }
+    if (threadIdx.x == SCAN_BLOCK - 1 && tile_sums) tile_sums[blockIdx.x] = excl;
+}
+__global__ void k_scan_add(int64_t *out, int64_t n, const int64_t *tile_offsets) {
+    int64_t i = (int64_t)blockIdx.x * SCAN_TILE + threadIdx.x;
+    int64_t add = tile_offsets[blockIdx.x];
+    for (int k = 0; k < SCAN_ITEMS; k++, i += SCAN_BLOCK)
+        if (i < n) out[i] += add;
+}
+static void scan_rec(Ctx *ctx, const int64_t *in, int64_t *out, int64_t n, int64_t *total_dev) {
+    int64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (tiles <= 1) {
+        k_scan_tiles<<<1, SCAN_BLOCK, 0, ctx->stream>>>(in, out, n, total_dev);
+        note_launch(ctx);
+        return;
+    }
+    DevBuf sums(ctx, (size_t)tiles * 8), offs(ctx, (size_t)tiles * 8);
+    k_scan_tiles<<<(int)tiles, SCAN_BLOCK, 0, ctx->stream>>>(in, out, n, sums.as<int64_t>());
+    note_launch(ctx);
+    scan_rec(ctx, sums.as<int64_t>(), offs.as<int64_t>(), tiles, total_dev);
+    k_scan_add<<<(int)tiles, SCAN_BLOCK, 0, ctx->stream>>>(out, n, offs.as<int64_t>());
+    note_launch(ctx);
+}
+void exclusive_scan_i64(Ctx *ctx, const int64_t *in, int64_t *out, int64_t n, int64_t *total_host) {
+    if (n == 0) {
+        if (total_host) *total_host = 0;
+        return;
+    }
+    DevBuf total(ctx, 8, true);
+    scan_rec(ctx, in, out, n, total.as<int64_t>());
+    if (total_host) {
+        DF_CUDA(cudaMemcpyAsync(total_host, total.ptr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        DF_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// import (Arrow C Data Interface -> HBM)
+// ------------------------------------------------------------------------------------------------
+static const void *upload(Ctx *ctx, DevCol &c, const void *src, size_t bytes, bool on_device) {
+    if (bytes == 0 || !src) return nullptr;
+    if (on_device) return src;
+    // 16 bytes of slack so vector loads at the tail stay in bounds
+    BufRef b = make_buf(ctx, bytes + 16);
+    DF_CUDA(cudaMemcpyAsync(b->ptr, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->h2d_bytes += (int64_t)bytes;
+    c.owned.push_back(b);
+    return b->ptr;
+}
+
+static ColRef import_array(Ctx *ctx, const ArrowArray *a, const TypeInfo &t, bool on_device) {
+    auto col = std::make_shared<DevCol>();
+    DevCol &c = *col;
+    c.type = t;
+    c.length = a->length;
+    int64_t off = a->offset, n = a->length;
+    const uint8_t *val = a->n_buffers > 0 ? (const uint8_t *)a->buffers[0] : nullptr;
+    c.null_count = a->null_count;
+    if (val && a->null_count != 0 && n > 0) {
+        int64_t b0 = off >> 3, b1 = (off + n + 7) >> 3;
+        c.validity = (const uint8_t *)upload(ctx, c, val + b0, (size_t)(b1 - b0), on_device);
+        c.vbit = (int32_t)(off & 7);
+        if (c.null_count < 0) c.null_count = -1;
+    } else {
+        c.null_count = 0;
+    }
+    int32_t phys = t.id == T_DICT ? t.index_id : t.id;
+    int w = type_width(phys);
+    if (phys == T_BOOL) {
+        if (a->n_buffers < 2) fail(DFGPU_INTERNAL, "boolean array without values buffer");
+        if (n > 0) {
+            int64_t b0 = off >> 3, b1 = (off + n + 7) >> 3;
+            c.values = upload(ctx, c, (const uint8_t *)a->buffers[1] + b0, (size_t)(b1 - b0), on_device);
+            c.dbit = (int32_t)(off & 7);
+        }
+    } else if (w > 0) {
+        if (a->n_buffers < 2) fail(DFGPU_INTERNAL, "primitive array without values buffer");
+        if (n > 0) c.values = upload(ctx, c, (const uint8_t *)a->buffers[1] + off * w, (size_t)(n * w), on_device);
+    } else if (t.is_var()) {
+        if (a->n_buffers < 3) fail(DFGPU_INTERNAL, "variable-width array needs 3 buffers");
+        int ow = t.is_large() ? 8 : 4;
+        const uint8_t *ho = (const uint8_t *)a->buffers[1] + off * ow;
+        int64_t first = 0, last = 0;
+        if (n > 0 || a->buffers[1]) {
+            if (on_device) {
+                uint8_t tmp[16];
+                DF_CUDA(cudaMemcpy(tmp, ho, ow, cudaMemcpyDeviceToHost));
+                DF_CUDA(cudaMemcpy(tmp + 8, ho + n * ow, ow, cudaMemcpyDeviceToHost));
+                first = ow == 8 ? *(int64_t *)tmp : *(int32_t *)tmp;
+                last = ow == 8 ? *(int64_t *)(tmp + 8) : *(int32_t *)(tmp + 8);
+            } else {
+                first = ow == 8 ? ((const int64_t *)ho)[0] : ((const int32_t *)ho)[0];
+                last = ow == 8 ? ((const int64_t *)ho)[n] : ((const int32_t *)ho)[n];
+            }
+            c.offsets = upload(ctx, c, ho, (size_t)((n + 1) * ow), on_device);
+        }
+        c.data_bytes = last - first;
+        const uint8_t *hd = (const uint8_t *)a->buffers[2];
+        if (on_device) {
+            c.values = hd;  // device data base already matches the offsets
+        } else if (last > first) {
+            const uint8_t *dd = (const uint8_t *)upload(ctx, c, hd + first, (size_t)(last - first), false);
+            c.values = dd - first;
+        }
+        if (!c.values) {
+            // zero data bytes: any non-null base works
+            BufRef b = make_buf(ctx, 16, true);
+            c.owned.push_back(b);
+            c.values = (const uint8_t *)b->ptr - first;
+        }
+    } else {
+        fail(DFGPU_NOT_IMPLEMENTED, "This feature is not implemented: import of type " + t.describe());
+    }
+    if (t.id == T_DICT) {
+        if (!a->dictionary) fail(DFGPU_INTERNAL, "dictionary array without dictionary");
+        c.dict = import_array(ctx, a->dictionary, *t.value, on_device);
+    }
+    return col;
+}
+
+Batch *batch_import(Ctx *ctx, const ArrowArray *arr, const Schema &schema, bool on_device) {
+    if (!arr) fail(DFGPU_INTERNAL, "null ArrowArray");
+    if (arr->n_children != (int64_t)schema.fields.size())
+        fail(DFGPU_INTERNAL, "RecordBatch has " + std::to_string(arr->n_children) + " columns, schema has " +
+                                 std::to_string(schema.fields.size()));
+    if (arr->offset != 0) fail(DFGPU_NOT_IMPLEMENTED, "struct-level offset on an imported RecordBatch");
+    std::unique_ptr<Batch> b(new Batch());
+    b->ctx = ctx;
+    b->num_rows = arr->length;
+    for (int64_t i = 0; i < arr->n_children; i++) {
+        const ArrowArray *ch = arr->children[i];
+        if (ch->length != arr->length) fail(DFGPU_INTERNAL, "column length mismatch in RecordBatch");
+        b->cols.push_back(import_array(ctx, ch, schema.fields[(size_t)i], on_device));
+    }
+    return b.release();
+}
+
+// ------------------------------------------------------------------------------------------------
+// export (HBM -> pinned host buffers, released by the consumer through ArrowArray.release)
+// ------------------------------------------------------------------------------------------------
+struct ArrayPriv {
+    std::vector<void *> pinned;  // owned host buffers
+    std::vector<const void *> buffers;
+    std::vector<ArrowArray> child_store;
+    std::vector<ArrowArray *> child_ptrs;
+    ArrowArray dict;
+    bool has_dict = false;
+};
+static void release_array(ArrowArray *a) {
+    if (!a || !a->release) return;
+    auto *p = (ArrayPriv *)a->private_data;
+    for (auto &c : p->child_store)
+        if (c.release) c.release(&c);
+    if (p->has_dict && p->dict.release) p->dict.release(&p->dict);
+    for (void *h : p->pinned) pinned_free(h);
+    delete p;
+    a->release = nullptr;
+}
+static const void *download(Ctx *ctx, ArrayPriv *p, const void *dev, size_t bytes) {
+    size_t alloc = bytes ? bytes : 8;
+    void *h = pinned_alloc(alloc);
+    p->pinned.push_back(h);
+    if (bytes) {
+        DF_CUDA(cudaMemcpyAsync(h, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        ctx->d2h_bytes += (int64_t)bytes;
+    } else {
+        memset(h, 0, alloc);
+    }
+    return h;
+}
+
+static void export_array(Ctx *ctx, const DevCol &c, ArrowArray *out, std::vector<BufRef> &temps,
+                         std::vector<std::pair<ArrowArray *, BufRef>> &pending_nulls) {
+    auto *p = new ArrayPriv();
+    memset(out, 0, sizeof *out);
+    out->private_data = p;
+    out->release = release_array;
+    int64_t n = c.length;
+    out->length = n;
+    out->offset = 0;
+    // validity (re-aligned to bit 0)
+    const void *hval = nullptr;
+    out->null_count = 0;
+    if (c.validity && c.null_count != 0 && n > 0) {
+        size_t words = (size_t)((n + 31) / 32);
+        const uint8_t *src = c.validity;
+        if (c.vbit != 0) {
+            BufRef t = make_buf(ctx, words * 4);
+            k_bitmap_realign<<<grid_for((int64_t)words, 256, ctx, 8), 256, 0, ctx->stream>>>(t->as<uint32_t>(), c.validity, c.vbit, n);
+            note_launch(ctx);
+            temps.push_back(t);
+            src = t->as<uint8_t>();
+        }
+        hval = download(ctx, p, src, (size_t)((n + 7) / 8));
+        if (c.null_count < 0) {
+            BufRef cnt = make_buf(ctx, 8, true);
+            k_count_unset<<<grid_for(n, 256, ctx, 8), 256, 0, ctx->stream>>>(c.validity, c.vbit, n, cnt->as<unsigned long long>());
+            note_launch(ctx);
+            pending_nulls.emplace_back(out, cnt);
+        } else {
+            out->null_count = c.null_count;
+        }
+    }
+    p->buffers.push_back(hval);
+    int32_t phys = c.type.id == T_DICT ? c.type.index_id : c.type.id;
+    int w = type_width(phys);
+    if (phys == T_BOOL) {
+        const uint8_t *src = (const uint8_t *)c.values;
+        size_t words = (size_t)((n + 31) / 32);
+        if (c.dbit != 0 && n > 0) {
+            BufRef t = make_buf(ctx, words * 4);
+            k_bitmap_realign<<<grid_for((int64_t)words, 256, ctx, 8), 256, 0, ctx->stream>>>(t->as<uint32_t>(), src, c.dbit, n);
+            note_launch(ctx);
+            temps.push_back(t);
+            src = t->as<uint8_t>();
+        }
+        p->buffers.push_back(download(ctx, p, src, (size_t)((n + 7) / 8)));
+    } else if (w > 0) {
+        p->buffers.push_back(download(ctx, p, c.values, (size_t)(n * w)));
+    } else if (c.type.is_var()) {
+        int ow = c.type.is_large() ? 8 : 4;
+        // rebase offsets to start at zero
+        int64_t first = 0;
+        if (n > 0) {
+            uint8_t tmp[8] = {0};
+            DF_CUDA(cudaMemcpyAsync(tmp, c.offsets, ow, cudaMemcpyDeviceToHost, ctx->stream));
+            DF_CUDA(cudaStreamSynchronize(ctx->stream));
+            first = ow == 8 ? *(int64_t *)tmp : *(int32_t *)tmp;
+        }
+        if (n == 0) {
+            void *h = pinned_alloc(16);
+            memset(h, 0, 16);
+            p->pinned.push_back(h);
+            p->buffers.push_back(h);
+        } else if (first != 0) {
+            BufRef t = make_buf(ctx, (size_t)((n + 1) * ow));
+            if (ow == 8)
+                k_rebase_offsets64<<<grid_for(n + 1, 256, ctx, 8), 256, 0, ctx->stream>>>(t->as<int64_t>(), (const int64_t *)c.offsets, n + 1, first, 0);
+            else
+                k_rebase_offsets32<<<grid_for(n + 1, 256, ctx, 8), 256, 0, ctx->stream>>>(t->as<int32_t>(), (const int32_t *)c.offsets, n + 1, first, 0);
+            note_launch(ctx);
+            temps.push_back(t);
+            p->buffers.push_back(download(ctx, p, t->ptr, (size_t)((n + 1) * ow)));
+        } else {
+            p->buffers.push_back(download(ctx, p, c.offsets, (size_t)((n + 1) * ow)));
+        }
+        p->buffers.push_back(download(ctx, p, (const uint8_t *)c.values + first, (size_t)c.data_bytes));
+    } else {
+        fail(DFGPU_NOT_IMPLEMENTED, "export of type " + c.type.describe());
+    }
+    if (c.type.id == T_DICT) {
+        p->has_dict = true;
+        export_array(ctx, *c.dict, &p->dict, temps, pending_nulls);
+        out->dictionary = &p->dict;
+    }
+    out->n_buffers = (int64_t)p->buffers.size();
+    out->buffers = p->buffers.data();
+}
+
+void batch_export(Ctx *ctx, const Batch *b, ArrowArray *out, ArrowSchema *out_schema) {
+    auto *p = new ArrayPriv();
+    memset(out, 0, sizeof *out);
+    out->private_data = p;
+    out->release = release_array;
+    out->length = b->num_rows;
+    p->buffers.push_back(nullptr);
+    out->n_buffers = 1;
+    out->buffers = p->buffers.data();
+    p->child_store.resize(b->cols.size());
+    std::vector<BufRef> temps;
+    std::vector<std::pair<ArrowArray *, BufRef>> pending_nulls;
+    try {
+        for (size_t i = 0; i < b->cols.size(); i++) {
+            export_array(ctx, *b->cols[i], &p->child_store[i], temps, pending_nulls);
+        }
+        std::vector<unsigned long long> counts(pending_nulls.size());
+        for (size_t i = 0; i < pending_nulls.size(); i++)
+            DF_CUDA(cudaMemcpyAsync(&counts[i], pending_nulls[i].second->ptr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        DF_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (size_t i = 0; i < pending_nulls.size(); i++) pending_nulls[i].first->null_count = (int64_t)counts[i];
+    } catch (...) {
+        release_array(out);
+        throw;
+    }
+    for (auto &c : p->child_store) p->child_ptrs.push_back(&c);
+    out->n_children = (int64_t)p->child_ptrs.size();
+    out->children = p->child_ptrs.data();
+    if (out_schema) schema_to_arrow(b->schema(), out_schema);
+}
+
+// ------------------------------------------------------------------------------------------------
+// nulls / slice / dictionary decode / take / concat
+// ------------------------------------------------------------------------------------------------
+ColRef col_nulls(Ctx *ctx, const TypeInfo &t, int64_t n) {  // new_null_array (joins/utils.rs:1209-1214)
+    auto c = std::make_shared<DevCol>();
+    c->type = t;
+    c->length = n;
+    c->null_count = n;
+    size_t vb = (size_t)((n + 31) / 32) * 4;
+    BufRef v = make_buf(ctx, vb + 16, true);
+    c->owned.push_back(v);
+    c->validity = v->as<uint8_t>();
+    int32_t phys = t.id == T_DICT ? t.index_id : t.id;
+    int w = type_width(phys);
+    if (phys == T_BOOL) {
+        BufRef b = make_buf(ctx, vb + 16, true);
+        c->owned.push_back(b);
+        c->values = b->ptr;
+    } else if (w > 0) {
+        BufRef b = make_buf(ctx, (size_t)(n * w) + 16, true);
+        c->owned.push_back(b);
+        c->values = b->ptr;
+    } else {
+        int ow = t.is_large() ? 8 : 4;
+        BufRef o = make_buf(ctx, (size_t)((n + 1) * ow) + 16, true);
+        BufRef d = make_buf(ctx, 16, true);
+        c->owned.push_back(o);
+        c->owned.push_back(d);
+        c->offsets = o->ptr;
+        c->values = d->ptr;
+        c->data_bytes = 0;
+    }
+    if (t.id == T_DICT) {
+        // empty dictionary; every index is NULL
+        auto d = std::make_shared<DevCol>();
+        d->type = *t.value;
+        d->length = 0;
+        if (d->type.is_var()) {
+            BufRef o = make_buf(ctx, 32, true);
+            d->owned.push_back(o);
+            d->offsets = o->ptr;
+            d->values = o->as<uint8_t>() + 16;
+        }
+        c->dict = d;
+    }
+    return c;
+}
+
+static ColRef col_slice(const ColRef &src, int64_t off, int64_t len, std::shared_ptr<void> keep) {
+    auto c = std::make_shared<DevCol>(*src);
+    c->length = len;
+    c->keepalive = keep;
+    if (src->validity) {
+        int64_t bit = src->vbit + off;
+        c->validity = src->validity + (bit >> 3);
+        c->vbit = (int32_t)(bit & 7);
+        c->null_count = (off == 0 && len == src->length) ? src->null_count : -1;
+    }
+    int32_t phys = src->type.id == T_DICT ? src->type.index_id : src->type.id;
+    int w = type_width(phys);
+    if (phys == T_BOOL) {
+        int64_t bit = src->dbit + off;
+        c->values = (const uint8_t *)src->values + (bit >> 3);
+        c->dbit = (int32_t)(bit & 7);
+    } else if (w > 0) {
+        c->values = (const uint8_t *)src->values + off * w;
+    } else {
+        int ow = src->type.is_large() ? 8 : 4;
+        c->offsets = (const uint8_t *)src->offsets + off * ow;
+        // data_bytes is an upper bound for a slice (exact value needs the offsets)
+    }
+    return c;
+}
+
+Batch *batch_slice(Ctx *ctx, const Batch *b, int64_t off, int64_t len) {
+    if (off < 0 || len < 0 || off + len > b->num_rows) fail(DFGPU_INTERNAL, "slice out of bounds");
+    std::unique_ptr<Batch> o(new Batch());
+    o->ctx = ctx;
+    o->num_rows = len;
+    for (auto &c : b->cols) {
+        ColRef s = col_slice(c, off, len, nullptr);
+        if (s->type.is_var() && len != c->length) {
+            // exact byte count of the slice
+            int ow = s->type.is_large() ? 8 : 4;
+            uint8_t t0[8] = {0}, t1[8] = {0};
+            DF_CUDA(cudaMemcpyAsync(t0, s->offsets, ow, cudaMemcpyDeviceToHost, ctx->stream));
+            DF_CUDA(cudaMemcpyAsync(t1, (const uint8_t *)s->offsets + len * ow, ow, cudaMemcpyDeviceToHost, ctx->stream));
+            DF_CUDA(cudaStreamSynchronize(ctx->stream));
+            int64_t f = ow == 8 ? *(int64_t *)t0 : *(int32_t *)t0, l = ow == 8 ? *(int64_t *)t1 : *(int32_t *)t1;
+            s->data_bytes = l - f;
+        }
+        o->cols.push_back(s);
+    }
+    return o.release();
+}
+
+// ---- take ------------------------------------------------------------------------------------------
+template <int W>
+__global__ void k_take_fixed(const uint8_t *__restrict__ src, ColView sv, const int64_t *__restrict__ idx, int64_t n,
+                             uint8_t *__restrict__ dst, uint32_t *__restrict__ out_valid) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t nround = (n + 31) / 32 * 32;
+    for (; i < nround; i += stride) {
+        bool valid = false;
+        if (i < n) {
+            int64_t j = idx[i];
+            valid = j >= 0 && col_valid(sv, j);
+            if (W == 16) {
+                uint4 v = valid ? *(const uint4 *)(src + 16 * j) : make_uint4(0, 0, 0, 0);
+                *(uint4 *)(dst + 16 * i) = v;
+            } else if (W == 8) {
+                ((uint64_t *)dst)[i] = valid ? ((const uint64_t *)src)[j] : 0;
+            } else if (W == 4) {
+                ((uint32_t *)dst)[i] = valid ? ((const uint32_t *)src)[j] : 0;
+            } else if (W == 2) {
+                ((uint16_t *)dst)[i] = valid ? ((const uint16_t *)src)[j] : 0;
+            } else {
+                dst[i] = valid ? src[j] : 0;
+            }
+        }
+        uint32_t m = __ballot_sync(0xffffffffu, valid);
+        if ((threadIdx.x & 31) == 0 && out_valid) out_valid[i >> 5] = m;
+    }
+}
+__global__ void k_take_bool(ColView sv, const int64_t *__restrict__ idx, int64_t n, uint32_t *__restrict__ dst,
+                            uint32_t *__restrict__ out_valid) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t nround = (n + 31) / 32 * 32;
+    for (; i < nround; i += stride) {
+        bool valid = false, v = false;
+        if (i < n) {
+            int64_t j = idx[i];
+            valid = j >= 0 && col_valid(sv, j);
+            v = valid && bit_get((const uint8_t *)sv.values, sv.dbit + j);
+        }
+        uint32_t m = __ballot_sync(0xffffffffu, valid), b = __ballot_sync(0xffffffffu, v);
+        if ((threadIdx.x & 31) == 0) {
+            dst[i >> 5] = b;
+            if (out_valid) out_valid[i >> 5] = m;
+        }
+    }
+}
+__global__ void k_take_lengths(ColView sv, const int64_t *__restrict__ idx, int64_t n, int64_t *__restrict__ lens,
+                               uint32_t *__restrict__ out_valid) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t nround = (n + 31) / 32 * 32;
+    for (; i < nround; i += stride) {
+        bool valid = false;
+        if (i < n) {
+            int64_t j = idx[i];
+            valid = j >= 0 && col_valid(sv, j);
+            int64_t len = 0;
+            if (valid) {
+                const uint8_t *p;
+                col_bytes(sv, j, p, len);
+            }
+            lens[i] = len;
+        }
+        uint32_t m = __ballot_sync(0xffffffffu, valid);
+        if ((threadIdx.x & 31) == 0 && out_valid) out_valid[i >> 5] = m;
+    }
+}
+// one warp per row copies the bytes; offsets written in the requested width
+__global__ void k_take_bytes(ColView sv, const int64_t *__restrict__ idx, int64_t n, const int64_t *__restrict__ starts,
+                             uint8_t *__restrict__ data, void *__restrict__ out_offsets, int large, int64_t total) {
+    int lane = threadIdx.x & 31;
+    int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t i = w; i < n; i += nw) {
+        int64_t j = idx[i];
+        int64_t st = starts[i];
+        if (lane == 0) {
+            if (large) ((int64_t *)out_offsets)[i] = st; else ((int32_t *)out_offsets)[i] = (int32_t)st;
+            if (i == n - 1) {
+                if (large) ((int64_t *)out_offsets)[n] = total; else ((int32_t *)out_offsets)[n] = (int32_t)total;
+            }
+        }
+        if (j >= 0 && col_valid(sv, j)) {
+            const uint8_t *p; int64_t len;
+            col_bytes(sv, j, p, len);
+            for (int64_t k = lane; k < len; k += 32) data[st + k] = p[k];
+        }
+    }
+}
+
+ColRef col_take(Ctx *ctx, const DevCol &src, const int64_t *idx, int64_t n, bool idx_may_be_null) {
+    auto c = std::make_shared<DevCol>();
+    c->type = src.type;
+    c->length = n;
+    bool need_valid = idx_may_be_null || (src.validity && src.null_count != 0);
+    size_t vwords = (size_t)((n + 31) / 32);
+    uint32_t *ov = nullptr;
+    if (need_valid) {
+        BufRef v = make_buf(ctx, vwords * 4 + 16, true);
+        c->owned.push_back(v);
+        ov = v->as<uint32_t>();
+        c->validity = v->as<uint8_t>();
+        c->null_count = -1;
+    }
+    ColView sv = src.view();
+    int32_t phys = src.type.id == T_DICT ? src.type.index_id : src.type.id;
+    int w = type_width(phys);
+    int grid = grid_for(n, 256, ctx, 16);
+    if (n == 0) {
+        // nothing to gather; still need legal buffers
+        if (src.type.is_var()) {
+            BufRef o = make_buf(ctx, 32, true);
+            c->owned.push_back(o);
+            c->offsets = o->ptr;
+            c->values = o->as<uint8_t>() + 16;
+        }
+        c->dict = src.dict;
+        return c;
+    }
+    if (phys == T_BOOL) {
+        BufRef b = make_buf(ctx, vwords * 4 + 16, true);
+        c->owned.push_back(b);
+        k_take_bool<<<grid, 256, 0, ctx->stream>>>(sv, idx, n, b->as<uint32_t>(), ov);
+        c->values = b->ptr;
+    } else if (w > 0) {
+        BufRef b = make_buf(ctx, (size_t)(n * w) + 16);
+        c->owned.push_back(b);
+        const uint8_t *s = (const uint8_t *)src.values;
+        uint8_t *d = b->as<uint8_t>();
+        switch (w) {
+        case 1: k_take_fixed<1><<<grid, 256, 0, ctx->stream>>>(s, sv, idx, n, d, ov); break;
+        case 2: k_take_fixed<2><<<grid, 256, 0, ctx->stream>>>(s, sv, idx, n, d, ov); break;
+        case 4: k_take_fixed<4><<<grid, 256, 0, ctx->stream>>>(s, sv, idx, n, d, ov); break;
+        case 8: k_take_fixed<8><<<grid, 256, 0, ctx->stream>>>(s, sv, idx, n, d, ov); break;
+        default: k_take_fixed<16><<<grid, 256, 0, ctx->stream>>>(s, sv, idx, n, d, ov); break;
+        }
+        c->values = b->ptr;
+    } else {
+        BufRef lens = make_buf(ctx, (size_t)n * 8), starts = make_buf(ctx, (size_t)n * 8);
+        k_take_lengths<<<grid, 256, 0, ctx->stream>>>(sv, idx, n, lens->as<int64_t>(), ov);
+        note_launch(ctx);
+        int64_t total = 0;
+        exclusive_scan_i64(ctx, lens->as<int64_t>(), starts->as<int64_t>(), n, &total);
+        if (!src.type.is_large() && total > 0x7fffffffLL)
+            fail(DFGPU_EXECUTION, "offset overflow: gathered Utf8/Binary data exceeds i32 offsets");  // binary_map.rs:464-471
+        int ow = src.type.is_large() ? 8 : 4;
+        BufRef o = make_buf(ctx, (size_t)((n + 1) * ow) + 16), d = make_buf(ctx, (size_t)total + 16);
+        c->owned.push_back(o);
+        c->owned.push_back(d);
+        k_take_bytes<<<grid_for(n * 32, 256, ctx, 16), 256, 0, ctx->stream>>>(sv, idx, n, starts->as<int64_t>(), d->as<uint8_t>(),
+                                                                             o->ptr, src.type.is_large() ? 1 : 0, total);
+        c->offsets = o->ptr;
+        c->values = d->ptr;
+        c->data_bytes = total;
+    }
+    note_launch(ctx);
+    c->dict = src.dict;
+    return c;
+}
+
+__global__ void k_dict_to_idx(ColView sv, ColView dv, int64_t n, int64_t *idx) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t j = -1;
+        if (col_valid(sv, i)) {
+            j = dict_index(sv, i);
+            if (!col_valid(dv, j)) j = -1;
+        }
+        idx[i] = j;
+    }
+}
+ColRef col_decode_dictionary(Ctx *ctx, const DevCol &src) {
+    if (src.type.id != T_DICT) fail(DFGPU_INTERNAL, "col_decode_dictionary on a non-dictionary column");
+    BufRef idx = make_buf(ctx, (size_t)src.length * 8 + 8);
+    if (src.length) {
+        k_dict_to_idx<<<grid_for(src.length, 256, ctx, 16), 256, 0, ctx->stream>>>(src.view(), src.dict->view(), src.length, idx->as<int64_t>());
+        note_launch(ctx);
+    }
+    ColRef out = col_take(ctx, *src.dict, idx->as<int64_t>(), src.length, true);
+    out->type.name = src.type.name;
+    out->type.nullable = src.type.nullable;
+    return out;
+}
+
+static ColRef col_concat(Ctx *ctx, const std::vector<ColRef> &parts, int64_t total) {
+    const DevCol &first = *parts[0];
+    if (first.type.id == T_DICT) {
+        bool same = true;
+        for (auto &p : parts) same = same && p->dict.get() == first.dict.get();
+        std::vector<ColRef> plain;
+        if (!same) {
+            // decode, concatenate, and wrap in a trivial dictionary (indices = 0..n-1) to keep the type
+            for (auto &p : parts) plain.push_back(col_decode_dictionary(ctx, *p));
+            ColRef vals = col_concat(ctx, plain, total);
+            auto c = std::make_shared<DevCol>();
+            c->type = first.type;
+            c->length = total;
+            int iw = type_width(first.type.index_id);
+            TypeInfo it; it.id = first.type.index_id;
+            double maxv = iw == 8 ? 9.2e18 : (double)((1ULL << (8 * iw - (it.is_signed_int() ? 1 : 0))) - 1);
+            if ((double)total > maxv) fail(DFGPU_NOT_IMPLEMENTED, "dictionary index type too narrow to concatenate dictionaries");
+            BufRef ib = make_buf(ctx, (size_t)(total * iw) + 16);
+            if (total) {
+                k_iota<<<grid_for(total, 256, ctx, 16), 256, 0, ctx->stream>>>(ib->ptr, iw, total);
+                note_launch(ctx);
+            }
+            c->owned.push_back(ib);
+            c->values = ib->ptr;
+            c->validity = vals->validity;
+            c->vbit = vals->vbit;
+            c->null_count = vals->null_count;
+            auto d = std::make_shared<DevCol>(*vals);
+            d->validity = nullptr; d->null_count = 0;  // nulls live on the indices
+            d->type.name = first.type.value->name;
+            c->dict = d;
+            c->keepalive = vals;
+            return c;
+        }
+    }
+    auto c = std::make_shared<DevCol>();
+    c->type = first.type;
+    c->length = total;
+    c->dict = first.dict;
+    bool any_nulls = false;
+    for (auto &p : parts) any_nulls = any_nulls || (p->validity && p->null_count != 0);
+    size_t vwords = (size_t)((total + 31) / 32);
+    if (any_nulls) {
+        BufRef v = make_buf(ctx, vwords * 4 + 16, true);
+        c->owned.push_back(v);
+        c->validity = v->as<uint8_t>();
+        int64_t pos = 0;
+        c->null_count = 0;
+        for (auto &p : parts) {
+            if (p->length) {
+                bool allv = !(p->validity && p->null_count != 0);
+                k_bitmap_append<<<grid_for(p->length, 256, ctx, 16), 256, 0, ctx->stream>>>(v->as<uint32_t>(), pos, p->validity, p->vbit, p->length, allv ? 1 : 0);
+                note_launch(ctx);
+            }
+            if (p->null_count < 0 || c->null_count < 0) c->null_count = -1; else c->null_count += p->null_count;
+            pos += p->length;
+        }
+    }
+    int32_t phys = first.type.id == T_DICT ? first.type.index_id : first.type.id;
+    int w = type_width(phys);
+    if (phys == T_BOOL) {
+        BufRef b = make_buf(ctx, vwords * 4 + 16, true);
+        c->owned.push_back(b);
+        int64_t pos = 0;
+        for (auto &p : parts) {
+            if (p->length) {
+                k_bitmap_append<<<grid_for(p->length, 256, ctx, 16), 256, 0, ctx->stream>>>(b->as<uint32_t>(), pos, (const uint8_t *)p->values, p->dbit, p->length, 0);
+                note_launch(ctx);
+            }
+            pos += p->length;
+        }
+        c->values = b->ptr;
+    } else if (w > 0) {
+        BufRef b = make_buf(ctx, (size_t)(total * w) + 16);
+        c->owned.push_back(b);
+        int64_t pos = 0;
+        for (auto &p : parts) {
+            if (p->length) DF_CUDA(cudaMemcpyAsync(b->as<uint8_t>() + pos * w, p->values, (size_t)(p->length * w), cudaMemcpyDeviceToDevice, ctx->stream));
+            pos += p->length;
+        }
+        c->values = b->ptr;
+    } else {
+        int ow = first.type.is_large() ? 8 : 4;
+        // per-part first offsets (host) to rebase
+        std::vector<int64_t> firsts(parts.size(), 0), lasts(parts.size(), 0);
+        std::vector<uint8_t> tmp(parts.size() * 16, 0);
+        for (size_t k = 0; k < parts.size(); k++) {
+            if (!parts[k]->length) continue;
+            DF_CUDA(cudaMemcpyAsync(&tmp[k * 16], parts[k]->offsets, ow, cudaMemcpyDeviceToHost, ctx->stream));
+            DF_CUDA(cudaMemcpyAsync(&tmp[k * 16 + 8], (const uint8_t *)parts[k]->offsets + parts[k]->length * ow, ow, cudaMemcpyDeviceToHost, ctx->stream));
+        }
+        DF_CUDA(cudaStreamSynchronize(ctx->stream));
+        int64_t bytes = 0;
+        for (size_t k = 0; k < parts.size(); k++) {
+            if (!parts[k]->length) continue;
+            firsts[k] = ow == 8 ? *(int64_t *)&tmp[k * 16] : *(int32_t *)&tmp[k * 16];
+            lasts[k] = ow == 8 ? *(int64_t *)&tmp[k * 16 + 8] : *(int32_t *)&tmp[k * 16 + 8];
+            bytes += lasts[k] - firsts[k];
+        }
+        if (ow == 4 && bytes > 0x7fffffffLL) fail(DFGPU_EXECUTION, "offset overflow concatenating Utf8/Binary data");
+        BufRef o = make_buf(ctx, (size_t)((total + 1) * ow) + 16, true), d = make_buf(ctx, (size_t)bytes + 16);
+        c->owned.push_back(o);
+        c->owned.push_back(d);
+        int64_t pos = 0, bpos = 0;
+        for (size_t k = 0; k < parts.size(); k++) {
+            auto &p = parts[k];
+            if (!p->length) continue;
+            if (ow == 8)
+                k_rebase_offsets64<<<grid_for(p->length + 1, 256, ctx, 16), 256, 0, ctx->stream>>>(o->as<int64_t>() + pos, (const int64_t *)p->offsets, p->length + 1, firsts[k], bpos);
+            else
+                k_rebase_offsets32<<<grid_for(p->length + 1, 256, ctx, 16), 256, 0, ctx->stream>>>(o->as<int32_t>() + pos, (const int32_t *)p->offsets, p->length + 1, firsts[k], bpos);
+            note_launch(ctx);
+            if (lasts[k] > firsts[k])
+                DF_CUDA(cudaMemcpyAsync(d->as<uint8_t>() + bpos, (const uint8_t *)p->values + firsts[k], (size_t)(lasts[k] - firsts[k]), cudaMemcpyDeviceToDevice, ctx->stream));
+            pos += p->length;
+            bpos += lasts[k] - firsts[k];
+        }
+        c->offsets = o->ptr;
+        c->values = d->ptr;
+        c->data_bytes = bytes;
+    }
+    return c;
+}
+
+Batch *batch_concat(Ctx *ctx, Batch *const *batches, int n) {
+    if (n <= 0) fail(DFGPU_INTERNAL, "concat of zero batches");
+    std::unique_ptr<Batch> o(new Batch());
+    o->ctx = ctx;
+    size_t nc = batches[0]->cols.size();
+    int64_t total = 0;
+    for (int i = 0; i < n; i++) {
+        if (batches[i]->cols.size() != nc) fail(DFGPU_INTERNAL, "concat: column count mismatch");
+        total += batches[i]->num_rows;
+    }
+    o->num_rows = total;
+    for (size_t c = 0; c < nc; c++) {
+        std::vector<ColRef> parts;
+        for (int i = 0; i < n; i++) parts.push_back(batches[i]->cols[c]);
+        if (n == 1) o->cols.push_back(parts[0]);
+        else o->cols.push_back(col_concat(ctx, parts, total));
+    }
+    return o.release();
+}
+
+}  // namespace dfgpu

@@ -1,0 +1,208 @@
+// common.h — host-side plumbing shared by every translation unit of libdfgpu:
+// status/exception bridge, context (device, stream, memory pools, NCCL), device buffers,
+// Arrow type descriptors, device-resident columns and RecordBatches.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/dfgpu.h"
+
+namespace dfgpu {
+
+// ------------------------------------------------------------------------------------------------
+// errors: C++ exceptions inside, status codes + thread-local message at the ABI
+// ------------------------------------------------------------------------------------------------
+struct Error {
+    dfgpu_status code;
+    std::string msg;
+};
+[[noreturn]] inline void fail(dfgpu_status code, const std::string &msg) { throw Error{code, msg}; }
+void set_last_error(const std::string &m);
+const std::string &last_error();
+void *pinned_alloc(size_t n);
+void pinned_free(void *p);
+
+#define DF_CUDA(expr)                                                                              \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess)                                                                     \
+            ::dfgpu::fail(DFGPU_CUDA, std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " + \
+                                          __FILE__ + ":" + std::to_string(__LINE__));              \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// types
+// ------------------------------------------------------------------------------------------------
+enum TypeId : int32_t {
+    T_BOOL = 1, T_I8, T_I16, T_I32, T_I64, T_U8, T_U16, T_U32, T_U64, T_F32, T_F64, T_DATE32, T_DATE64,
+    T_TS, T_TIME32, T_TIME64, T_DEC128, T_UTF8, T_LARGE_UTF8, T_BINARY, T_LARGE_BINARY, T_DICT
+};
+
+struct TypeInfo {
+    int32_t id = 0;
+    int32_t precision = 0, scale = 0;
+    std::string format;  // Arrow C format string (kept verbatim for pass-through types)
+    std::string name;
+    bool nullable = true;
+    bool dict_ordered = false;
+    int32_t index_id = 0;             // T_DICT: type id of the indices
+    std::shared_ptr<TypeInfo> value;  // T_DICT: value type
+
+    int width() const;  // fixed byte width, 0 for bool / var-width / dict
+    bool is_var() const { return id == T_UTF8 || id == T_LARGE_UTF8 || id == T_BINARY || id == T_LARGE_BINARY; }
+    bool is_large() const { return id == T_LARGE_UTF8 || id == T_LARGE_BINARY; }
+    bool is_signed_int() const {
+        return id == T_I8 || id == T_I16 || id == T_I32 || id == T_I64 || id == T_DATE32 || id == T_DATE64 ||
+               id == T_TS || id == T_TIME32 || id == T_TIME64;
+    }
+    bool is_unsigned_int() const { return id == T_U8 || id == T_U16 || id == T_U32 || id == T_U64; }
+    bool is_float() const { return id == T_F32 || id == T_F64; }
+    const TypeInfo &value_type() const { return id == T_DICT ? *value : *this; }
+    std::string describe() const;
+};
+int type_width(int32_t id);
+TypeInfo type_from_schema(const ArrowSchema *s);
+TypeInfo make_type(int32_t id, const std::string &name, bool nullable = true, int precision = 0, int scale = 0);
+std::string format_of(const TypeInfo &t);
+
+struct Schema {
+    std::vector<TypeInfo> fields;
+};
+Schema schema_from_arrow(const ArrowSchema *s);  // "+s" struct schema -> fields
+void schema_to_arrow(const Schema &s, ArrowSchema *out);
+
+// ------------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------------
+struct PinnedPool {
+    std::mutex mu;
+    std::multimap<size_t, void *> free_list;
+    std::map<void *, size_t> sizes;
+    size_t cached = 0;
+    void *alloc(size_t bytes);
+    void release(void *p);
+    void trim();
+};
+
+}  // namespace dfgpu
+
+struct dfgpu_ctx {
+    dfgpu_options opts;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    int sm_count = 148;
+    size_t smem_optin = 0;
+    int64_t launches = 0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0, nvlink_bytes = 0;
+    void *nccl_comm = nullptr;  // ncclComm_t
+    dfgpu::PinnedPool pinned;
+    uint64_t *flush_dummy = nullptr;
+};
+
+namespace dfgpu {
+typedef dfgpu_ctx Ctx;
+
+// device buffer allocated from the stream-ordered pool of ctx->stream
+struct DevBuf {
+    Ctx *ctx = nullptr;
+    void *ptr = nullptr;
+    size_t bytes = 0;
+    DevBuf() {}
+    DevBuf(Ctx *c, size_t n, bool zero = false);
+    ~DevBuf();
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    template <class T> T *as() const { return (T *)ptr; }
+};
+typedef std::shared_ptr<DevBuf> BufRef;
+inline BufRef make_buf(Ctx *c, size_t n, bool zero = false) { return std::make_shared<DevBuf>(c, n, zero); }
+
+// POD view handed to kernels
+struct ColView {
+    const uint8_t *validity;  // bitmap or nullptr
+    const void *values;       // fixed: element 0; bool: bitmap; var: data base; dict: indices
+    const void *offsets;      // var: offsets of element 0
+    int64_t vbit;             // bit offset of row 0 in validity
+    int64_t dbit;             // bool: bit offset of row 0 in values
+    int32_t type;             // TypeId of this physical array (T_DICT for dictionary)
+    int32_t width;            // fixed width (index width for dict)
+    int32_t large;            // var: 64-bit offsets
+    int32_t index_signed;     // dict
+};
+
+// device-resident Arrow array
+struct DevCol {
+    TypeInfo type;
+    int64_t length = 0;
+    int64_t null_count = 0;
+    const uint8_t *validity = nullptr;
+    int64_t vbit = 0;
+    const void *values = nullptr;
+    int64_t dbit = 0;
+    const void *offsets = nullptr;
+    int64_t data_bytes = 0;          // var-width: bytes referenced by this column
+    std::shared_ptr<DevCol> dict;    // dictionary values
+    std::vector<BufRef> owned;       // keeps device memory alive
+    std::shared_ptr<void> keepalive; // e.g. parent batch for slices
+
+    ColView view() const;
+};
+typedef std::shared_ptr<DevCol> ColRef;
+
+}  // namespace dfgpu
+
+struct dfgpu_batch {
+    dfgpu::Ctx *ctx = nullptr;
+    int64_t num_rows = 0;
+    std::vector<dfgpu::ColRef> cols;
+    dfgpu::Schema schema() const {
+        dfgpu::Schema s;
+        for (auto &c : cols) s.fields.push_back(c->type);
+        return s;
+    }
+};
+
+namespace dfgpu {
+typedef dfgpu_batch Batch;
+
+// ---- batch.cu ----
+Batch *batch_import(Ctx *ctx, const ArrowArray *arr, const Schema &schema, bool on_device);
+void batch_export(Ctx *ctx, const Batch *b, ArrowArray *out, ArrowSchema *out_schema);
+Batch *batch_concat(Ctx *ctx, Batch *const *batches, int n);
+Batch *batch_slice(Ctx *ctx, const Batch *b, int64_t off, int64_t len);
+// gather rows (compute::take); idx < 0 => NULL row.  idx is a device array of n int64.
+ColRef col_take(Ctx *ctx, const DevCol &src, const int64_t *idx, int64_t n, bool idx_may_be_null);
+ColRef col_nulls(Ctx *ctx, const TypeInfo &t, int64_t n);
+ColRef col_decode_dictionary(Ctx *ctx, const DevCol &src);  // Dictionary -> plain value type
+int64_t count_nulls(Ctx *ctx, const uint8_t *validity, int64_t vbit, int64_t n);
+// view of rows [off, off+len) of a column view
+inline ColView view_at(ColView v, int64_t off) {
+    v.vbit += off;
+    if (v.type == T_BOOL) v.dbit += off;
+    else if (v.offsets) v.offsets = (const uint8_t *)v.offsets + off * (v.large ? 8 : 4);
+    else v.values = (const uint8_t *)v.values + off * v.width;
+    return v;
+}
+// exclusive prefix sum of n int64 (device -> device); returns total via *total_host if non-null
+void exclusive_scan_i64(Ctx *ctx, const int64_t *in, int64_t *out, int64_t n, int64_t *total_host);
+
+// launch helper: counts launches for bench.py "gpu_launches"
+inline void note_launch(Ctx *ctx, int n = 1) { ctx->launches += n; }
+inline int grid_for(int64_t n, int block, Ctx *ctx, int max_waves = 64) {
+    int64_t g = (n + block - 1) / block;
+    int64_t cap = (int64_t)ctx->sm_count * max_waves;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+}  // namespace dfgpu

@@ -1,0 +1,423 @@
+// join.cu — HashJoinExec on the device (physical-plan/src/joins/hash_join.rs, joins/utils.rs).
+//   build  : collect_left_input (hash_join.rs:678-768) — concat the build batches, intern the
+//            key of every build row to a dense key id (GroupTable), then lay the row ids of each
+//            key out contiguously (count -> scan -> fill) instead of JoinHashMap's `next` chains
+//            (utils.rs:121-229): span[key] = (start, count), rows[start .. start+count).
+//   probe  : lookup_join_hashmap + equal_rows_arr (hash_join.rs:1024-1118) fused — the table is
+//            keyed by the real key, so there are no false candidates to filter — as the two-pass
+//            count -> exclusive scan -> scatter of (build_idx, probe_idx) pairs, with the
+//            join-type index fix-ups of adjust_indices_by_join_type (utils.rs:1234-1279) folded
+//            into the count/scatter, then build_batch_from_indices (utils.rs:1180-1230) = take.
+//   final  : process_unmatched_build_batch / get_final_indices_from_bit_map
+//            (hash_join.rs:1348-1388, utils.rs:1119-1141) from the visited flags.
+#include <chrono>
+
+#include "device.cuh"
+#include "groups.h"
+
+struct dfgpu_join {
+    dfgpu::Ctx *ctx = nullptr;
+    int join_type = 0, partition_mode = 0;
+    bool null_equals_null = false;
+    dfgpu::Schema build_schema, probe_schema, out_schema;
+    std::vector<int> bkeys, pkeys;
+    std::vector<std::unique_ptr<dfgpu_batch>> pending;  // build batches until build_finish
+    std::unique_ptr<dfgpu_batch> build;
+    std::unique_ptr<dfgpu::GroupTable> table;
+    dfgpu::BufRef span, rows, visited, gid_scratch;
+    int64_t build_rows = 0, num_keys = 0;
+    bool finished = false;
+    dfgpu_metrics m;
+};
+
+namespace dfgpu {
+typedef dfgpu_join JoinOp;
+
+static bool need_final(int jt) {  // need_produce_result_in_final (utils.rs:1103-1108)
+    return jt == DFGPU_JOIN_LEFT || jt == DFGPU_JOIN_LEFT_ANTI || jt == DFGPU_JOIN_LEFT_SEMI || jt == DFGPU_JOIN_FULL;
+}
+
+__global__ void k_build_count(TableView t, const uint32_t *__restrict__ gids, int64_t n, uint32_t *__restrict__ cnt) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t g = resolve_gid(t, gids[i]);
+        if (g != GID_NONE) atomicAdd(&cnt[g], 1u);
+    }
+}
+__global__ void k_fill_none(uint32_t *p, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = GID_NONE;
+}
+__global__ void k_u32_to_i64(const uint32_t *in, int64_t n, int64_t *out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = in[i];
+}
+__global__ void k_make_span(const int64_t *__restrict__ starts, const uint32_t *__restrict__ cnt, int64_t G, uint64_t *__restrict__ span,
+                            uint32_t *__restrict__ cursor) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < G; i += (int64_t)gridDim.x * blockDim.x) {
+        span[i] = ((uint64_t)starts[i] << 32) | cnt[i];
+        cursor[i] = 0;
+    }
+}
+__global__ void k_build_fill(TableView t, const uint32_t *__restrict__ gids, int64_t n, const uint64_t *__restrict__ span,
+                             uint32_t *__restrict__ cursor, uint32_t *__restrict__ rows) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t g = resolve_gid(t, gids[i]);
+        if (g == GID_NONE) continue;
+        uint32_t pos = atomicAdd(&cursor[g], 1u);
+        rows[(span[g] >> 32) + pos] = (uint32_t)i;
+    }
+}
+
+// pass 1: output rows per probe row for this join type
+__global__ void k_probe_count(const uint32_t *__restrict__ gids, int64_t n, const uint64_t *__restrict__ span, int jt,
+                              int64_t *__restrict__ counts) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t g = gids[i];
+        int64_t c = g == GID_NONE ? 0 : (int64_t)(uint32_t)span[g];
+        int64_t o;
+        switch (jt) {
+        case DFGPU_JOIN_INNER: case DFGPU_JOIN_LEFT: o = c; break;
+        case DFGPU_JOIN_RIGHT: case DFGPU_JOIN_FULL: o = c ? c : 1; break;  // + unmatched probe rows (utils.rs:1248-1254)
+        case DFGPU_JOIN_RIGHT_SEMI: o = c ? 1 : 0; break;                   // get_semi_indices
+        case DFGPU_JOIN_RIGHT_ANTI: o = c ? 0 : 1; break;                   // get_anti_indices
+        default: o = 0; break;                                              // LeftSemi / LeftAnti: produced at the end
+        }
+        counts[i] = o;
+    }
+}
+// pass 2: scatter (build_idx, probe_idx) pairs; mark visited build rows (hash_join.rs:1274-1278)
+__global__ void k_probe_scatter(const uint32_t *__restrict__ gids, int64_t n, const uint64_t *__restrict__ span,
+                                const uint32_t *__restrict__ rows, const int64_t *__restrict__ offs, int jt,
+                                int64_t *__restrict__ out_build, int64_t *__restrict__ out_probe, uint8_t *__restrict__ visited) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t g = gids[i];
+        uint64_t sp = g == GID_NONE ? 0 : span[g];
+        uint32_t c = (uint32_t)sp;
+        uint64_t st = sp >> 32;
+        int64_t o = offs[i];
+        switch (jt) {
+        case DFGPU_JOIN_INNER: case DFGPU_JOIN_LEFT: case DFGPU_JOIN_RIGHT: case DFGPU_JOIN_FULL:
+            for (uint32_t k = 0; k < c; k++) {
+                uint32_t r = rows[st + k];
+                out_build[o + k] = r;
+                out_probe[o + k] = i;
+                if (visited) visited[r] = 1;
+            }
+            if (c == 0 && (jt == DFGPU_JOIN_RIGHT || jt == DFGPU_JOIN_FULL)) { out_build[o] = -1; out_probe[o] = i; }
+            break;
+        case DFGPU_JOIN_RIGHT_SEMI: if (c) out_probe[o] = i; break;
+        case DFGPU_JOIN_RIGHT_ANTI: if (!c) out_probe[o] = i; break;
+        default:  // LeftSemi / LeftAnti: only the visited flags
+            for (uint32_t k = 0; k < c; k++) visited[rows[st + k]] = 1;
+            break;
+        }
+    }
+}
+__global__ void k_flags_to_counts(const uint8_t *__restrict__ flags, int64_t n, int want, int64_t *__restrict__ out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (flags[i] != 0) == (want != 0) ? 1 : 0;
+}
+__global__ void k_compact(const int64_t *__restrict__ counts, const int64_t *__restrict__ offs, int64_t n, int64_t *__restrict__ out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        if (counts[i]) out[offs[i]] = i;
+}
+
+static TypeInfo forced_nullable(TypeInfo t) {
+    t.nullable = true;
+    return t;
+}
+
+JoinOp *join_create(Ctx *ctx, int jt, int pmode, bool null_eq, const Schema &bs, const Schema &ps, const int32_t *bk, const int32_t *pk, int nk) {
+    std::unique_ptr<JoinOp> j(new JoinOp());
+    j->ctx = ctx;
+    j->join_type = jt;
+    j->partition_mode = pmode;
+    j->null_equals_null = null_eq;
+    j->build_schema = bs;
+    j->probe_schema = ps;
+    memset(&j->m, 0, sizeof j->m);
+    if (jt < 0 || jt > DFGPU_JOIN_RIGHT_ANTI) fail(DFGPU_PLAN, "unknown JoinType");
+    if (nk <= 0) fail(DFGPU_PLAN, "On constraints in HashJoinExec should be non-empty");  // hash_join.rs:320-322
+    std::vector<TypeInfo> key_types;
+    for (int i = 0; i < nk; i++) {
+        if (bk[i] < 0 || bk[i] >= (int)bs.fields.size() || pk[i] < 0 || pk[i] >= (int)ps.fields.size())
+            fail(DFGPU_PLAN, "join key column index out of range");
+        const TypeInfo &l = bs.fields[bk[i]].value_type(), &r = ps.fields[pk[i]].value_type();
+        bool both_str = (l.id == T_UTF8 || l.id == T_LARGE_UTF8) && (r.id == T_UTF8 || r.id == T_LARGE_UTF8);
+        bool both_bin = (l.id == T_BINARY || l.id == T_LARGE_BINARY) && (r.id == T_BINARY || r.id == T_LARGE_BINARY);
+        if (l.id != r.id && !both_str && !both_bin)
+            fail(DFGPU_PLAN, "join key types differ: " + l.describe() + " vs " + r.describe());  // check_join_is_valid
+        j->bkeys.push_back(bk[i]);
+        j->pkeys.push_back(pk[i]);
+        // the table is declared with plain value types: dictionary keys are interned by value
+        TypeInfo kt = l;
+        if (bs.fields[bk[i]].id == T_DICT || ps.fields[pk[i]].id == T_DICT) {
+            // force the packed (multi-column style) path so both encodings meet in one string table
+            kt = l;
+        }
+        key_types.push_back(kt);
+    }
+    j->table.reset(new GroupTable(ctx, key_types));
+    // build_join_schema (utils.rs:657-729)
+    bool left_null = jt == DFGPU_JOIN_RIGHT || jt == DFGPU_JOIN_FULL;
+    bool right_null = jt == DFGPU_JOIN_LEFT || jt == DFGPU_JOIN_FULL;
+    bool left_out = jt != DFGPU_JOIN_RIGHT_SEMI && jt != DFGPU_JOIN_RIGHT_ANTI;
+    bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
+    if (left_out) for (auto &f : bs.fields) j->out_schema.fields.push_back(left_null ? forced_nullable(f) : f);
+    if (right_out) for (auto &f : ps.fields) j->out_schema.fields.push_back(right_null ? forced_nullable(f) : f);
+    return j.release();
+}
+
+void join_build_push(JoinOp &j, const Batch &b) {
+    if (j.finished) fail(DFGPU_INTERNAL, "build side already finished");
+    if (b.cols.size() != j.build_schema.fields.size()) fail(DFGPU_INTERNAL, "build batch does not match the build schema");
+    std::unique_ptr<Batch> copy(new Batch(b));  // shares column buffers
+    j.m.build_input_batches += 1;
+    j.m.build_input_rows += b.num_rows;
+    j.pending.push_back(std::move(copy));
+}
+
+// key columns for interning: dictionary-encoded keys are decoded so both sides present plain values
+static std::vector<ColRef> key_columns(Ctx *ctx, const Batch &b, const std::vector<int> &idx) {
+    std::vector<ColRef> out;
+    for (int c : idx) {
+        ColRef col = b.cols[c];
+        if (col->type.id == T_DICT) col = col_decode_dictionary(ctx, *col);
+        out.push_back(col);
+    }
+    return out;
+}
+
+static void intern_chunks(JoinOp &j, const std::vector<ColRef> &keys, int64_t n, uint32_t *gids, bool find_only) {
+    Ctx *ctx = j.ctx;
+    std::vector<const DevCol *> kp;
+    for (auto &k : keys) kp.push_back(k.get());
+    int64_t chunk = ctx->opts.chunk_rows > 0 ? ctx->opts.chunk_rows : (4LL << 20);
+    NullPolicy np = j.null_equals_null ? NULLS_ARE_KEYS : NULLS_EXCLUDED;  // eq vs not_distinct (hash_join.rs:1067-1076)
+    for (int64_t off = 0; off < n; off += chunk) {
+        int64_t m = std::min(chunk, n - off);
+        j.table->intern(kp, off, m, gids + off, find_only, np);
+    }
+}
+
+void join_build_finish(JoinOp &j) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    auto t0 = std::chrono::steady_clock::now();
+    if (j.finished) return;
+    std::vector<Batch *> bs;
+    for (auto &p : j.pending) bs.push_back(p.get());
+    if (bs.empty()) {
+        j.build.reset(new Batch());
+        j.build->ctx = ctx;
+        for (auto &f : j.build_schema.fields) j.build->cols.push_back(col_nulls(ctx, f, 0));
+    } else {
+        j.build.reset(batch_concat(ctx, bs.data(), (int)bs.size()));  // concat_batches (hash_join.rs:764)
+    }
+    j.pending.clear();
+    int64_t nb = j.build->num_rows;
+    if (nb >= (1LL << 32) - 1) fail(DFGPU_RESOURCES_EXHAUSTED, "Resources exhausted: build side larger than 2^32 rows");
+    j.build_rows = nb;
+    if (nb) {
+        BufRef gids = make_buf(ctx, (size_t)nb * 4 + 16);
+        std::vector<ColRef> keys = key_columns(ctx, *j.build, j.bkeys);
+        intern_chunks(j, keys, nb, gids->as<uint32_t>(), false);
+        int64_t G = j.table->num_groups_sync();
+        j.num_keys = G;
+        TableView tv = j.table->view();
+        BufRef cnt = make_buf(ctx, (size_t)G * 4 + 16, true), cnt64 = make_buf(ctx, (size_t)G * 8 + 16), starts = make_buf(ctx, (size_t)G * 8 + 16);
+        j.span = make_buf(ctx, (size_t)G * 8 + 16);
+        j.rows = make_buf(ctx, (size_t)nb * 4 + 16);
+        int grid = grid_for(nb, 256, ctx, 32);
+        k_build_count<<<grid, 256, 0, st>>>(tv, gids->as<uint32_t>(), nb, cnt->as<uint32_t>());
+        if (G) {
+            k_u32_to_i64<<<grid_for(G, 256, ctx, 32), 256, 0, st>>>(cnt->as<uint32_t>(), G, cnt64->as<int64_t>());
+            exclusive_scan_i64(ctx, cnt64->as<int64_t>(), starts->as<int64_t>(), G, nullptr);
+            // cnt64 is reused as the 32-bit fill cursor
+            k_make_span<<<grid_for(G, 256, ctx, 32), 256, 0, st>>>(starts->as<int64_t>(), cnt->as<uint32_t>(), G, j.span->as<uint64_t>(), cnt64->as<uint32_t>());
+            k_build_fill<<<grid, 256, 0, st>>>(tv, gids->as<uint32_t>(), nb, j.span->as<uint64_t>(), cnt64->as<uint32_t>(), j.rows->as<uint32_t>());
+            note_launch(ctx, 3);
+        }
+        note_launch(ctx);
+        DF_CUDA(cudaGetLastError());
+    }
+    if (need_final(j.join_type)) j.visited = make_buf(ctx, (size_t)nb + 16, true);
+    j.finished = true;
+    j.m.build_mem_used = (int64_t)(j.table->device_bytes() + (j.span ? j.span->bytes : 0) + (j.rows ? j.rows->bytes : 0));
+    DF_CUDA(cudaStreamSynchronize(st));
+    j.m.build_time_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+}
+
+static Batch *empty_output(JoinOp &j) {
+    std::unique_ptr<Batch> o(new Batch());
+    o->ctx = j.ctx;
+    for (auto &f : j.out_schema.fields) o->cols.push_back(col_nulls(j.ctx, f, 0));
+    return o.release();
+}
+
+Batch *join_probe(JoinOp &j, const Batch &probe) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    auto t0 = std::chrono::steady_clock::now();
+    if (!j.finished) fail(DFGPU_INTERNAL, "probe before build_finish");
+    if (probe.cols.size() != j.probe_schema.fields.size()) fail(DFGPU_INTERNAL, "probe batch does not match the probe schema");
+    int64_t np = probe.num_rows;
+    j.m.input_batches += 1;
+    j.m.input_rows += np;
+    int jt = j.join_type;
+    if (np == 0) return empty_output(j);
+    BufRef gids = make_buf(ctx, (size_t)np * 4 + 16);
+    int grid = grid_for(np, 256, ctx, 32);
+    bool have_table = j.build_rows > 0 && j.num_keys > 0;
+    if (have_table) {
+        std::vector<ColRef> keys = key_columns(ctx, probe, j.pkeys);
+        intern_chunks(j, keys, np, gids->as<uint32_t>(), true);
+    } else {  // empty build side: every lookup misses (tests join_left_empty_right etc., hash_join.rs:2069-2140)
+        k_fill_none<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np);
+        note_launch(ctx);
+    }
+    BufRef counts = make_buf(ctx, (size_t)np * 8 + 16), offs = make_buf(ctx, (size_t)np * 8 + 16);
+    const uint64_t *span = have_table ? j.span->as<uint64_t>() : nullptr;
+    k_probe_count<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np, span, jt, counts->as<int64_t>());
+    note_launch(ctx);
+    int64_t total = 0;
+    exclusive_scan_i64(ctx, counts->as<int64_t>(), offs->as<int64_t>(), np, &total);
+    bool left_out = jt != DFGPU_JOIN_RIGHT_SEMI && jt != DFGPU_JOIN_RIGHT_ANTI;
+    bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
+    BufRef ob = make_buf(ctx, (size_t)total * 8 + 16), op = make_buf(ctx, (size_t)total * 8 + 16);
+    uint8_t *visited = j.visited ? j.visited->as<uint8_t>() : nullptr;
+    k_probe_scatter<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np, span, have_table ? j.rows->as<uint32_t>() : nullptr, offs->as<int64_t>(),
+                                          jt, ob->as<int64_t>(), op->as<int64_t>(), visited);
+    note_launch(ctx);
+    DF_CUDA(cudaGetLastError());
+    std::unique_ptr<Batch> out(new Batch());
+    out->ctx = ctx;
+    if (!right_out) {  // LeftSemi / LeftAnti emit nothing per probe batch (utils.rs:1269-1277)
+        out.reset(empty_output(j));
+    } else {
+        out->num_rows = total;
+        size_t fi = 0;
+        bool build_nullable = jt == DFGPU_JOIN_RIGHT || jt == DFGPU_JOIN_FULL;
+        if (left_out)
+            for (auto &c : j.build->cols) {
+                ColRef t = (j.build_rows == 0) ? col_nulls(ctx, c->type, total) : col_take(ctx, *c, ob->as<int64_t>(), total, build_nullable);
+                t->type = j.out_schema.fields[fi++];
+                out->cols.push_back(t);
+            }
+        for (auto &c : probe.cols) {
+            ColRef t = col_take(ctx, *c, op->as<int64_t>(), total, false);
+            t->type = j.out_schema.fields[fi++];
+            out->cols.push_back(t);
+        }
+    }
+    j.m.output_batches += 1;
+    j.m.output_rows += out->num_rows;
+    j.m.join_time_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+    return out.release();
+}
+
+Batch *join_emit_unmatched(JoinOp &j) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    if (!j.finished) fail(DFGPU_INTERNAL, "emit_unmatched before build_finish");
+    if (!need_final(j.join_type)) return nullptr;
+    int64_t nb = j.build_rows;
+    int jt = j.join_type;
+    int64_t total = 0;
+    BufRef idx = make_buf(ctx, 16);
+    if (nb) {
+        BufRef counts = make_buf(ctx, (size_t)nb * 8 + 16), offs = make_buf(ctx, (size_t)nb * 8 + 16);
+        int grid = grid_for(nb, 256, ctx, 32);
+        k_flags_to_counts<<<grid, 256, 0, st>>>(j.visited->as<uint8_t>(), nb, jt == DFGPU_JOIN_LEFT_SEMI ? 1 : 0, counts->as<int64_t>());
+        exclusive_scan_i64(ctx, counts->as<int64_t>(), offs->as<int64_t>(), nb, &total);
+        idx = make_buf(ctx, (size_t)total * 8 + 16);
+        k_compact<<<grid, 256, 0, st>>>(counts->as<int64_t>(), offs->as<int64_t>(), nb, idx->as<int64_t>());
+        note_launch(ctx, 2);
+        DF_CUDA(cudaGetLastError());
+    }
+    std::unique_ptr<Batch> out(new Batch());
+    out->ctx = ctx;
+    out->num_rows = total;
+    size_t fi = 0;
+    for (auto &c : j.build->cols) {
+        ColRef t = col_take(ctx, *c, idx->as<int64_t>(), total, false);
+        t->type = j.out_schema.fields[fi++];
+        out->cols.push_back(t);
+    }
+    if (jt == DFGPU_JOIN_LEFT || jt == DFGPU_JOIN_FULL)
+        for (auto &f : j.probe_schema.fields) {
+            (void)f;
+            out->cols.push_back(col_nulls(ctx, j.out_schema.fields[fi], total));
+            fi++;
+        }
+    j.m.output_batches += 1;
+    j.m.output_rows += total;
+    return out.release();
+}
+
+}  // namespace dfgpu
+
+using namespace dfgpu;
+#define J_TRY try {
+#define J_CATCH } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; } \
+    catch (const std::exception &e) { dfgpu::set_last_error(std::string("Internal error: ") + e.what()); return DFGPU_INTERNAL; } \
+    return DFGPU_OK;
+
+extern "C" {
+dfgpu_status dfgpu_join_create(dfgpu_ctx *ctx, int32_t join_type, int32_t partition_mode, int32_t null_equals_null,
+                               const ArrowSchema *build_schema, const ArrowSchema *probe_schema, const int32_t *build_keys,
+                               const int32_t *probe_keys, int32_t n_keys, dfgpu_join **out) {
+    J_TRY
+    DF_CUDA(cudaSetDevice(ctx->device));
+    *out = join_create(ctx, join_type, partition_mode, null_equals_null != 0, schema_from_arrow(build_schema), schema_from_arrow(probe_schema),
+                       build_keys, probe_keys, n_keys);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_output_schema(const dfgpu_join *join, ArrowSchema *out) {
+    J_TRY
+    schema_to_arrow(join->out_schema, out);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_build_push(dfgpu_join *join, const dfgpu_batch *batch) {
+    J_TRY
+    join_build_push(*join, *batch);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_build_finish(dfgpu_join *join) {
+    J_TRY
+    DF_CUDA(cudaSetDevice(join->ctx->device));
+    join_build_finish(*join);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_probe(dfgpu_join *join, const dfgpu_batch *probe, dfgpu_batch **out) {
+    J_TRY
+    DF_CUDA(cudaSetDevice(join->ctx->device));
+    *out = join_probe(*join, *probe);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_emit_unmatched(dfgpu_join *join, dfgpu_batch **out) {
+    J_TRY
+    DF_CUDA(cudaSetDevice(join->ctx->device));
+    *out = join_emit_unmatched(*join);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_metrics(const dfgpu_join *join, dfgpu_metrics *out) {
+    J_TRY
+    *out = join->m;
+    out->h2d_bytes = join->ctx->h2d_bytes;
+    out->d2h_bytes = join->ctx->d2h_bytes;
+    out->kernel_launches = join->ctx->launches;
+    J_CATCH
+}
+void dfgpu_join_destroy(dfgpu_join *join) {
+    if (!join) return;
+    cudaSetDevice(join->ctx->device);
+    delete join;
+}
+}

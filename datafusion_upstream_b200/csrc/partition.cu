@@ -1,0 +1,448 @@
+// partition.cu — RepartitionExec(Hash) on the device: BatchPartitioner::partition_iter
+// (physical-plan/src/repartition/mod.rs:162-217) as a stable multi-split, and the exchange itself
+// (the reference's per-partition channels, repartition/mod.rs:442-580, distributor_channels.rs)
+// as grouped ncclSend/ncclRecv all-to-all over NVLink.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+
+#include "device.cuh"
+#include "groups.h"
+
+namespace dfgpu {
+void create_hashes_device(Ctx *ctx, const std::vector<const DevCol *> &cols, int64_t row_off, int64_t n, uint64_t seed, uint64_t *out);
+
+static const int PART_T = 256;
+static const int MAX_PARTS = 1024;
+
+// pass 1: per-block histogram of hash % P over a contiguous row range
+__global__ void __launch_bounds__(PART_T) k_part_count(const uint64_t *__restrict__ hashes, int64_t n, int64_t rows_per_block, int P,
+                                                       uint32_t *__restrict__ pid, int64_t *__restrict__ hist /* [P][nblocks] */) {
+    extern __shared__ uint32_t cnt[];
+    for (int p = threadIdx.x; p < P; p += PART_T) cnt[p] = 0;
+    __syncthreads();
+    int64_t lo = (int64_t)blockIdx.x * rows_per_block, hi = min(n, lo + rows_per_block);
+    for (int64_t i = lo + threadIdx.x; i < hi; i += PART_T) {
+        uint32_t p = (uint32_t)(hashes[i] % (uint64_t)P);  // repartition/mod.rs:184-187
+        pid[i] = p;
+        atomicAdd(&cnt[p], 1u);
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < P; p += PART_T) hist[(int64_t)p * gridDim.x + blockIdx.x] = cnt[p];
+}
+// pass 2: stable scatter of row indices; rows keep input order inside each partition
+__global__ void __launch_bounds__(PART_T) k_part_scatter(const uint32_t *__restrict__ pid, int64_t n, int64_t rows_per_block, int P,
+                                                         const int64_t *__restrict__ starts /* [P][nblocks] */, int64_t *__restrict__ perm) {
+    extern __shared__ int64_t sm64[];
+    int64_t *base = sm64;                                 // [P] running cursor of this block
+    uint32_t *wcnt = (uint32_t *)(sm64 + P);              // [warps][P]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = PART_T / 32;
+    for (int p = threadIdx.x; p < P; p += PART_T) base[p] = starts[(int64_t)p * gridDim.x + blockIdx.x];
+    for (int k = threadIdx.x; k < nw * P; k += PART_T) wcnt[k] = 0;
+    __syncthreads();
+    int64_t lo = (int64_t)blockIdx.x * rows_per_block, hi = min(n, lo + rows_per_block);
+    for (int64_t s = lo; s < hi; s += PART_T) {
+        int64_t i = s + threadIdx.x;
+        bool in = i < hi;
+        uint32_t p = in ? pid[i] : 0xffffffffu;
+        uint32_t peers = __match_any_sync(0xffffffffu, p);
+        uint32_t rank = __popc(peers & ((1u << lane) - 1));
+        if (in && rank == 0) wcnt[warp * P + p] = __popc(peers);
+        __syncthreads();
+        if (in) {
+            int64_t off = base[p] + rank;
+            for (int w = 0; w < warp; w++) off += wcnt[w * P + p];
+            perm[off] = i;
+        }
+        __syncthreads();
+        for (int q = threadIdx.x; q < P; q += PART_T) {
+            uint32_t t = 0;
+            for (int w = 0; w < nw; w++) { t += wcnt[w * P + q]; wcnt[w * P + q] = 0; }
+            base[q] += t;
+        }
+        __syncthreads();
+    }
+}
+
+// returns perm (row indices grouped by partition, stable) and host offsets[P + 1]
+static BufRef partition_perm(Ctx *ctx, const Batch &b, const int32_t *key_cols, int n_keys, int P, std::vector<int64_t> &offsets) {
+    if (P <= 0 || P > MAX_PARTS) fail(DFGPU_NOT_IMPLEMENTED, "number of hash partitions must be in 1..1024");
+    std::vector<const DevCol *> keys;
+    for (int i = 0; i < n_keys; i++) {
+        if (key_cols[i] < 0 || key_cols[i] >= (int)b.cols.size()) fail(DFGPU_PLAN, "partition key column out of range");
+        keys.push_back(b.cols[key_cols[i]].get());
+    }
+    int64_t n = b.num_rows;
+    offsets.assign((size_t)P + 1, 0);
+    BufRef perm = make_buf(ctx, (size_t)n * 8 + 16);
+    if (n == 0) return perm;
+    cudaStream_t st = ctx->stream;
+    BufRef hashes = make_buf(ctx, (size_t)n * 8), pid = make_buf(ctx, (size_t)n * 4);
+    create_hashes_device(ctx, keys, 0, n, 0, hashes->as<uint64_t>());  // seeds (0,0,0,0): repartition/mod.rs:115
+    int nblocks = (int)std::min<int64_t>((n + 4095) / 4096, (int64_t)ctx->sm_count * 8);
+    int64_t rpb = (n + nblocks - 1) / nblocks;
+    rpb = (rpb + PART_T - 1) / PART_T * PART_T;
+    nblocks = (int)((n + rpb - 1) / rpb);
+    size_t hn = (size_t)P * nblocks;
+    BufRef hist = make_buf(ctx, hn * 8), starts = make_buf(ctx, hn * 8);
+    k_part_count<<<nblocks, PART_T, P * 4, st>>>(hashes->as<uint64_t>(), n, rpb, P, pid->as<uint32_t>(), hist->as<int64_t>());
+    note_launch(ctx);
+    exclusive_scan_i64(ctx, hist->as<int64_t>(), starts->as<int64_t>(), (int64_t)hn, nullptr);
+    size_t smem = (size_t)P * 8 + (size_t)(PART_T / 32) * P * 4;
+    if (smem > 48 * 1024) DF_CUDA(cudaFuncSetAttribute(k_part_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_part_scatter<<<nblocks, PART_T, smem, st>>>(pid->as<uint32_t>(), n, rpb, P, starts->as<int64_t>(), perm->as<int64_t>());
+    note_launch(ctx);
+    DF_CUDA(cudaGetLastError());
+    // partition p starts at starts[p][0]
+    std::vector<int64_t> first((size_t)P);
+    DF_CUDA(cudaMemcpy2DAsync(first.data(), 8, starts->ptr, (size_t)nblocks * 8, 8, (size_t)P, cudaMemcpyDeviceToHost, st));
+    DF_CUDA(cudaStreamSynchronize(st));
+    for (int p = 0; p < P; p++) offsets[(size_t)p] = first[(size_t)p];
+    offsets[(size_t)P] = n;
+    return perm;
+}
+
+void partition_hash(Ctx *ctx, const Batch &b, const int32_t *key_cols, int n_keys, int P, Batch **out_parts) {
+    std::vector<int64_t> off;
+    BufRef perm = partition_perm(ctx, b, key_cols, n_keys, P, off);
+    for (int p = 0; p < P; p++) {
+        out_parts[p] = nullptr;
+        int64_t cnt = off[(size_t)p + 1] - off[(size_t)p];
+        if (cnt == 0) continue;  // empty sub-batches are not produced (repartition/mod.rs:196-214)
+        std::unique_ptr<Batch> o(new Batch());
+        o->ctx = ctx;
+        o->num_rows = cnt;
+        for (auto &c : b.cols) o->cols.push_back(col_take(ctx, *c, perm->as<int64_t>() + off[(size_t)p], cnt, false));
+        out_parts[p] = o.release();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// NCCL (loaded lazily so single-GPU use has no NCCL dependency)
+// ------------------------------------------------------------------------------------------------
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi &nccl() {
+    static NcclApi api;
+    if (!api.lib) {
+        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        for (auto nm : names) {
+            api.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (api.lib) break;
+        }
+        if (!api.lib) fail(DFGPU_NCCL, std::string("cannot load libnccl: ") + dlerror());
+#define LOAD(f) \
+    *(void **)(&api.f) = dlsym(api.lib, "nccl" #f); \
+    if (!api.f) fail(DFGPU_NCCL, "libnccl lacks nccl" #f);
+        LOAD(GetUniqueId) LOAD(CommInitRank) LOAD(CommDestroy) LOAD(Send) LOAD(Recv) LOAD(GroupStart) LOAD(GroupEnd)
+        LOAD(AllGather) LOAD(GetErrorString)
+#undef LOAD
+    }
+    return api;
+}
+#define DF_NCCL(expr)                                                                                        \
+    do {                                                                                                     \
+        ncclResult_t _r = (expr);                                                                            \
+        if (_r != ncclSuccess) fail(DFGPU_NCCL, std::string("NCCL error: ") + nccl().GetErrorString(_r));   \
+    } while (0)
+
+void ctx_init_nccl(Ctx *ctx) {
+    if (!ctx->opts.nccl_unique_id) fail(DFGPU_PLAN, "world > 1 requires a ncclUniqueId");
+    ncclUniqueId id;
+    memcpy(&id, ctx->opts.nccl_unique_id, sizeof id);
+    ncclComm_t comm;
+    DF_NCCL(nccl().CommInitRank(&comm, ctx->opts.world, id, ctx->opts.rank));
+    ctx->nccl_comm = comm;
+}
+void ctx_destroy_nccl(Ctx *ctx) {
+    if (ctx->nccl_comm) nccl().CommDestroy((ncclComm_t)ctx->nccl_comm);
+    ctx->nccl_comm = nullptr;
+}
+
+// ---- exchange helpers --------------------------------------------------------------------------------
+__global__ void k_bitmap_to_bytes(const uint8_t *bm, int64_t bit0, int64_t n, uint8_t *out, int all_one) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = all_one ? 1 : (bit_get(bm, bit0 + i) ? 1 : 0);
+}
+__global__ void k_bytes_to_bits(const uint8_t *__restrict__ bytes, int64_t n, uint32_t *__restrict__ words) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int64_t nround = (n + 31) / 32 * 32;
+    for (; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t m = __ballot_sync(0xffffffffu, i < n && bytes[i] != 0);
+        if ((threadIdx.x & 31) == 0) words[i >> 5] = m;
+    }
+}
+__global__ void k_lengths_of(ColView v, int64_t n, int64_t *out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint8_t *p; int64_t len;
+        col_bytes(v, i, p, len);
+        out[i] = len;
+    }
+}
+__global__ void k_offsets_from_starts(const int64_t *starts, int64_t n, int64_t total, void *out, int large) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i <= n; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t v = i < n ? starts[i] : total;
+        if (large) ((int64_t *)out)[i] = v; else ((int32_t *)out)[i] = (int32_t)v;
+    }
+}
+__global__ void k_iota_p(void *dst, int width, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (width == 1) ((uint8_t *)dst)[i] = (uint8_t)i;
+        else if (width == 2) ((uint16_t *)dst)[i] = (uint16_t)i;
+        else if (width == 4) ((uint32_t *)dst)[i] = (uint32_t)i;
+        else ((uint64_t *)dst)[i] = (uint64_t)i;
+    }
+}
+static ColRef wrap_trivial_dictionary(Ctx *ctx, const ColRef &plain, const TypeInfo &dict_type) {
+    int64_t n = plain->length;
+    auto wrap = std::make_shared<DevCol>();
+    wrap->type = dict_type;
+    wrap->length = n;
+    int iw = type_width(dict_type.index_id);
+    TypeInfo it; it.id = dict_type.index_id;
+    double maxv = iw == 8 ? 9.2e18 : (double)((1ULL << (8 * iw - (it.is_signed_int() ? 1 : 0))) - 1);
+    if ((double)n > maxv) fail(DFGPU_EXECUTION, "dictionary index type too narrow");
+    BufRef ib = make_buf(ctx, (size_t)n * iw + 16);
+    if (n) { k_iota_p<<<grid_for(n, 256, ctx, 16), 256, 0, ctx->stream>>>(ib->ptr, iw, n); note_launch(ctx); }
+    wrap->owned.push_back(ib);
+    wrap->values = ib->ptr;
+    wrap->validity = plain->validity;
+    wrap->vbit = plain->vbit;
+    wrap->null_count = plain->null_count;
+    auto d = std::make_shared<DevCol>(*plain);
+    d->validity = nullptr; d->null_count = 0;
+    d->type = *dict_type.value;
+    wrap->dict = d;
+    wrap->keepalive = plain;
+    return wrap;
+}
+
+// The all-to-all.  Per column we ship: values (rows x width), validity as one byte per row,
+// var-width columns as (int64 length per row, bytes).  Counts go first (ncclAllGather).
+Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) {
+    int W = ctx->opts.world, me = ctx->opts.rank;
+    size_t nc = schema.fields.size();
+    if (W <= 1) {
+        if (!parts[0]) return nullptr;
+        Batch *one[1] = {parts[0]};
+        return batch_concat(ctx, one, 1);
+    }
+    ncclComm_t comm = (ncclComm_t)ctx->nccl_comm;
+    cudaStream_t st = ctx->stream;
+    // decode dictionaries; count rows / var bytes per destination
+    std::vector<std::vector<ColRef>> send((size_t)W, std::vector<ColRef>(nc));
+    size_t rec = 1 + 2 * nc;  // rows, then per column: var bytes, has_validity
+    std::vector<int64_t> mine((size_t)W * rec, 0);
+    for (int r = 0; r < W; r++) {
+        if (!parts[r]) continue;
+        if (parts[r]->cols.size() != nc) fail(DFGPU_INTERNAL, "exchange: schema mismatch");
+        mine[r * rec] = parts[r]->num_rows;
+        for (size_t c = 0; c < nc; c++) {
+            ColRef col = parts[r]->cols[c];
+            if (col->type.id == T_DICT) col = col_decode_dictionary(ctx, *col);
+            send[r][c] = col;
+            if (col->type.is_var()) mine[r * rec + 1 + 2 * c] = col->data_bytes;
+            mine[r * rec + 2 + 2 * c] = (col->validity && col->null_count != 0) ? 1 : 0;
+        }
+    }
+    size_t row_bytes = (size_t)W * rec * 8;
+    BufRef d_mine = make_buf(ctx, row_bytes), d_all = make_buf(ctx, row_bytes * W);
+    DF_CUDA(cudaMemcpyAsync(d_mine->ptr, mine.data(), row_bytes, cudaMemcpyHostToDevice, st));
+    DF_NCCL(nccl().AllGather(d_mine->ptr, d_all->ptr, row_bytes, ncclChar, comm, st));
+    std::vector<int64_t> all((size_t)W * W * rec);
+    DF_CUDA(cudaMemcpyAsync(all.data(), d_all->ptr, row_bytes * W, cudaMemcpyDeviceToHost, st));
+    DF_CUDA(cudaStreamSynchronize(st));
+    auto cnt = [&](int src, int dst, size_t k) { return all[((size_t)src * W + dst) * rec + k]; };
+    std::vector<int64_t> row_off((size_t)W + 1, 0);
+    for (int s = 0; s < W; s++) row_off[s + 1] = row_off[s] + cnt(s, me, 0);
+    int64_t total = row_off[W];
+    if (total == 0) {
+        // still take part in the collective with zero-sized transfers below? nothing to send/recv to me,
+        // but peers may expect data from me: fall through with empty receive buffers.
+    }
+    std::unique_ptr<Batch> out(new Batch());
+    out->ctx = ctx;
+    out->num_rows = total;
+    for (size_t c = 0; c < nc; c++) {
+        TypeInfo ft = schema.fields[c];
+        TypeInfo vt = ft.value_type();
+        vt.name = ft.name; vt.nullable = ft.nullable;
+        bool any_valid = false;
+        for (int s = 0; s < W; s++)
+            for (int d = 0; d < W; d++) any_valid = any_valid || cnt(s, d, 2 + 2 * c) != 0;
+        auto col = std::make_shared<DevCol>();
+        col->type = vt;
+        col->length = total;
+        std::vector<BufRef> keep;
+        // 1) validity bytes
+        BufRef rv;
+        if (any_valid) {
+            rv = make_buf(ctx, (size_t)total + 16);
+            std::vector<BufRef> sv((size_t)W);
+            for (int r = 0; r < W; r++) {
+                int64_t n = mine[r * rec];
+                sv[r] = make_buf(ctx, (size_t)n + 16);
+                if (n) {
+                    const ColRef &sc = send[r][c];
+                    bool allv = !(sc->validity && sc->null_count != 0);
+                    k_bitmap_to_bytes<<<grid_for(n, 256, ctx, 16), 256, 0, st>>>(sc->validity, sc->vbit, n, sv[r]->as<uint8_t>(), allv ? 1 : 0);
+                    note_launch(ctx);
+                }
+            }
+            DF_NCCL(nccl().GroupStart());
+            for (int r = 0; r < W; r++) {
+                if (mine[r * rec]) DF_NCCL(nccl().Send(sv[r]->ptr, (size_t)mine[r * rec], ncclChar, r, comm, st));
+                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rv->as<uint8_t>() + row_off[r], (size_t)cnt(r, me, 0), ncclChar, r, comm, st));
+            }
+            DF_NCCL(nccl().GroupEnd());
+            for (int r = 0; r < W; r++) if (r != me) ctx->nvlink_bytes += mine[r * rec];
+            BufRef bits = make_buf(ctx, (size_t)((total + 31) / 32) * 4 + 16, true);
+            if (total) { k_bytes_to_bits<<<grid_for(total, 256, ctx, 16), 256, 0, st>>>(rv->as<uint8_t>(), total, bits->as<uint32_t>()); note_launch(ctx); }
+            col->owned.push_back(bits);
+            col->validity = bits->as<uint8_t>();
+            col->null_count = -1;
+            keep.insert(keep.end(), sv.begin(), sv.end());
+        }
+        // 2) payload
+        int w = vt.width();
+        if (vt.id == T_BOOL) {
+            BufRef rb = make_buf(ctx, (size_t)total + 16);
+            std::vector<BufRef> sb((size_t)W);
+            for (int r = 0; r < W; r++) {
+                int64_t n = mine[r * rec];
+                sb[r] = make_buf(ctx, (size_t)n + 16);
+                if (n) { k_bitmap_to_bytes<<<grid_for(n, 256, ctx, 16), 256, 0, st>>>((const uint8_t *)send[r][c]->values, send[r][c]->dbit, n, sb[r]->as<uint8_t>(), 0); note_launch(ctx); }
+            }
+            DF_NCCL(nccl().GroupStart());
+            for (int r = 0; r < W; r++) {
+                if (mine[r * rec]) DF_NCCL(nccl().Send(sb[r]->ptr, (size_t)mine[r * rec], ncclChar, r, comm, st));
+                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rb->as<uint8_t>() + row_off[r], (size_t)cnt(r, me, 0), ncclChar, r, comm, st));
+            }
+            DF_NCCL(nccl().GroupEnd());
+            BufRef bits = make_buf(ctx, (size_t)((total + 31) / 32) * 4 + 16, true);
+            if (total) { k_bytes_to_bits<<<grid_for(total, 256, ctx, 16), 256, 0, st>>>(rb->as<uint8_t>(), total, bits->as<uint32_t>()); note_launch(ctx); }
+            col->owned.push_back(bits);
+            col->values = bits->ptr;
+            keep.insert(keep.end(), sb.begin(), sb.end());
+            keep.push_back(rb);
+        } else if (w > 0) {
+            BufRef rb = make_buf(ctx, (size_t)total * w + 16);
+            DF_NCCL(nccl().GroupStart());
+            for (int r = 0; r < W; r++) {
+                if (mine[r * rec]) DF_NCCL(nccl().Send(send[r][c]->values, (size_t)mine[r * rec] * w, ncclChar, r, comm, st));
+                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rb->as<uint8_t>() + row_off[r] * w, (size_t)cnt(r, me, 0) * w, ncclChar, r, comm, st));
+            }
+            DF_NCCL(nccl().GroupEnd());
+            for (int r = 0; r < W; r++) if (r != me) ctx->nvlink_bytes += mine[r * rec] * w;
+            col->owned.push_back(rb);
+            col->values = rb->ptr;
+        } else {
+            // lengths, then bytes
+            std::vector<int64_t> byte_off((size_t)W + 1, 0);
+            for (int s = 0; s < W; s++) byte_off[s + 1] = byte_off[s] + cnt(s, me, 1 + 2 * c);
+            int64_t tbytes = byte_off[W];
+            BufRef rl = make_buf(ctx, (size_t)total * 8 + 16), rd = make_buf(ctx, (size_t)tbytes + 16);
+            std::vector<BufRef> sl((size_t)W);
+            std::vector<int64_t> firsts((size_t)W, 0);
+            for (int r = 0; r < W; r++) {
+                int64_t n = mine[r * rec];
+                sl[r] = make_buf(ctx, (size_t)n * 8 + 16);
+                if (n) {
+                    k_lengths_of<<<grid_for(n, 256, ctx, 16), 256, 0, st>>>(send[r][c]->view(), n, sl[r]->as<int64_t>());
+                    note_launch(ctx);
+                    int ow = send[r][c]->type.is_large() ? 8 : 4;
+                    uint8_t t0[8] = {0};
+                    DF_CUDA(cudaMemcpyAsync(t0, send[r][c]->offsets, ow, cudaMemcpyDeviceToHost, st));
+                    DF_CUDA(cudaStreamSynchronize(st));
+                    firsts[r] = ow == 8 ? *(int64_t *)t0 : *(int32_t *)t0;
+                }
+            }
+            DF_NCCL(nccl().GroupStart());
+            for (int r = 0; r < W; r++) {
+                int64_t n = mine[r * rec], nb = mine[r * rec + 1 + 2 * c];
+                if (n) DF_NCCL(nccl().Send(sl[r]->ptr, (size_t)n * 8, ncclChar, r, comm, st));
+                if (nb) DF_NCCL(nccl().Send((const uint8_t *)send[r][c]->values + firsts[r], (size_t)nb, ncclChar, r, comm, st));
+                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rl->as<int64_t>() + row_off[r], (size_t)cnt(r, me, 0) * 8, ncclChar, r, comm, st));
+                if (cnt(r, me, 1 + 2 * c)) DF_NCCL(nccl().Recv(rd->as<uint8_t>() + byte_off[r], (size_t)cnt(r, me, 1 + 2 * c), ncclChar, r, comm, st));
+            }
+            DF_NCCL(nccl().GroupEnd());
+            for (int r = 0; r < W; r++) if (r != me) ctx->nvlink_bytes += mine[r * rec] * 8 + mine[r * rec + 1 + 2 * c];
+            BufRef starts = make_buf(ctx, (size_t)total * 8 + 16);
+            int64_t tot2 = 0;
+            exclusive_scan_i64(ctx, rl->as<int64_t>(), starts->as<int64_t>(), total, &tot2);
+            int ow = vt.is_large() ? 8 : 4;
+            if (ow == 4 && tbytes > 0x7fffffffLL) fail(DFGPU_EXECUTION, "offset overflow in exchanged Utf8/Binary column");
+            BufRef offs = make_buf(ctx, (size_t)(total + 1) * ow + 16, true);
+            k_offsets_from_starts<<<grid_for(total + 1, 256, ctx, 16), 256, 0, st>>>(starts->as<int64_t>(), total, tbytes, offs->ptr, ow == 8);
+            note_launch(ctx);
+            col->owned.push_back(offs);
+            col->owned.push_back(rd);
+            col->offsets = offs->ptr;
+            col->values = rd->ptr;
+            col->data_bytes = tbytes;
+            keep.insert(keep.end(), sl.begin(), sl.end());
+        }
+        DF_CUDA(cudaGetLastError());
+        ColRef result = col;
+        if (ft.id == T_DICT) result = wrap_trivial_dictionary(ctx, col, ft);
+        out->cols.push_back(result);
+        // send buffers are freed stream-ordered after the collective
+    }
+    if (total == 0) return nullptr;
+    return out.release();
+}
+
+}  // namespace dfgpu
+
+using namespace dfgpu;
+extern "C" {
+dfgpu_status dfgpu_nccl_get_unique_id(void *out128) {
+    try {
+        ncclUniqueId id;
+        DF_NCCL(nccl().GetUniqueId(&id));
+        memcpy(out128, &id, sizeof id);
+    } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; }
+    return DFGPU_OK;
+}
+dfgpu_status dfgpu_partition_hash(dfgpu_ctx *ctx, const dfgpu_batch *batch, const int32_t *key_cols, int32_t n_keys, int32_t n_parts,
+                                  dfgpu_batch **out_parts) {
+    try {
+        DF_CUDA(cudaSetDevice(ctx->device));
+        partition_hash(ctx, *batch, key_cols, n_keys, n_parts, out_parts);
+    } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; }
+    return DFGPU_OK;
+}
+dfgpu_status dfgpu_exchange_all_to_all(dfgpu_ctx *ctx, dfgpu_batch *const *parts, const ArrowSchema *schema, dfgpu_batch **out) {
+    try {
+        DF_CUDA(cudaSetDevice(ctx->device));
+        Schema s = schema_from_arrow(schema);
+        *out = exchange_all_to_all(ctx, parts, s);
+    } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; }
+    return DFGPU_OK;
+}
+dfgpu_status dfgpu_exchange_all_gather(dfgpu_ctx *ctx, const dfgpu_batch *local, const ArrowSchema *schema, dfgpu_batch **out) {
+    try {
+        DF_CUDA(cudaSetDevice(ctx->device));
+        Schema s = schema_from_arrow(schema);
+        int W = ctx->opts.world;
+        // all-gather == all-to-all where every destination receives the same local batch
+        std::vector<dfgpu_batch *> parts((size_t)std::max(1, W), const_cast<dfgpu_batch *>(local));
+        *out = exchange_all_to_all(ctx, parts.data(), s);
+    } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; }
+    return DFGPU_OK;
+}
+}

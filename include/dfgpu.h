@@ -1,0 +1,197 @@
+/*
+ * dfgpu.h — C ABI of the B200-native hash-aggregation / hash-join / hash-repartition path.
+ *
+ * This is the drop-in boundary for DataFusion 36's hash-table operator path.  Every entry point
+ * names the reference interface it replaces (paths relative to /root/reference/datafusion).
+ * RecordBatches cross the boundary through the Arrow C Data Interface (include/arrow_c_data.h):
+ * inputs are BORROWED for the duration of the call (the library copies them to HBM and never
+ * calls `release`); outputs are library-allocated pinned host buffers whose `release` callback
+ * frees them (standard producer semantics).
+ *
+ * Conventions
+ *   - every function returns a dfgpu_status; on failure dfgpu_last_error() (thread-local) holds
+ *     the message.  Codes mirror the DataFusionError variants used on this path
+ *     (common/src/error.rs; SURVEY §8b "Error convention").
+ *   - all handles are opaque; *_destroy / *_free accept NULL.
+ *   - no exceptions cross the ABI, no torch / C++ types in signatures.
+ *   - there is NO CPU fallback: without a CUDA device dfgpu_ctx_create fails with DFGPU_CUDA.
+ */
+#ifndef DFGPU_H
+#define DFGPU_H
+
+#include <stdint.h>
+#include "arrow_c_data.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t dfgpu_status;
+enum {
+    DFGPU_OK = 0,
+    DFGPU_INTERNAL = 1,            /* DataFusionError::Internal            */
+    DFGPU_PLAN = 2,                /* DataFusionError::Plan                */
+    DFGPU_EXECUTION = 3,           /* DataFusionError::Execution           */
+    DFGPU_RESOURCES_EXHAUSTED = 4, /* DataFusionError::ResourcesExhausted  */
+    DFGPU_NOT_IMPLEMENTED = 5,     /* DataFusionError::NotImplemented      */
+    DFGPU_CUDA = 6,
+    DFGPU_NCCL = 7
+};
+
+/* AggregateMode — physical-plan/src/aggregates/mod.rs:63-100 */
+enum {
+    DFGPU_AGG_PARTIAL = 0,
+    DFGPU_AGG_FINAL = 1,
+    DFGPU_AGG_FINAL_PARTITIONED = 2,
+    DFGPU_AGG_SINGLE = 3,
+    DFGPU_AGG_SINGLE_PARTITIONED = 4
+};
+/* the GroupsAccumulator implementations on the path */
+enum { DFGPU_SUM = 1, DFGPU_COUNT = 2, DFGPU_AVG = 3, DFGPU_MIN = 4, DFGPU_MAX = 5 };
+/* JoinType — common/src/join_type.rs:30-47 */
+enum {
+    DFGPU_JOIN_INNER = 0, DFGPU_JOIN_LEFT = 1, DFGPU_JOIN_RIGHT = 2, DFGPU_JOIN_FULL = 3,
+    DFGPU_JOIN_LEFT_SEMI = 4, DFGPU_JOIN_RIGHT_SEMI = 5, DFGPU_JOIN_LEFT_ANTI = 6,
+    DFGPU_JOIN_RIGHT_ANTI = 7
+};
+/* PartitionMode — physical-plan/src/joins/mod.rs:39-47 */
+enum { DFGPU_PARTITIONED = 0, DFGPU_COLLECT_LEFT = 1 };
+
+typedef struct dfgpu_ctx dfgpu_ctx;
+typedef struct dfgpu_batch dfgpu_batch;
+typedef struct dfgpu_agg dfgpu_agg;
+typedef struct dfgpu_join dfgpu_join;
+
+/* Options ~ the `gpu.*` ConfigOptions namespace (common/src/config.rs; SURVEY §5 "Config"). */
+typedef struct dfgpu_options {
+    int32_t device;                /* CUDA ordinal                                             */
+    int32_t batch_size;            /* datafusion.execution.batch_size (config.rs:215), 8192    */
+    int64_t memory_limit;          /* device bytes an operator may hold; 0 = unlimited
+                                      (MemoryPool, execution/src/memory_pool/mod.rs:83-108)    */
+    double load_factor;            /* hash-table load factor, default 0.5                      */
+    int32_t force_hash_collisions; /* cargo feature force_hash_collisions (hash_utils.rs:307)  */
+    int32_t rank, world;           /* this process' GPU rank / number of GPUs (1 = no NCCL)    */
+    const void *nccl_unique_id;    /* 128-byte ncclUniqueId shared by all ranks, or NULL       */
+    int64_t chunk_rows;            /* rows per internal launch wave, 0 = default (4 Mi)         */
+} dfgpu_options;
+
+typedef struct dfgpu_metrics {     /* BaselineMetrics + BuildProbeJoinMetrics
+                                      (physical-plan/src/metrics/baseline.rs:47-67,
+                                       joins/utils.rs:1368-1426)                               */
+    int64_t elapsed_compute_ns, output_rows, output_batches;
+    int64_t input_rows, input_batches;
+    int64_t build_input_rows, build_input_batches, build_mem_used, build_time_ns, join_time_ns;
+    int64_t h2d_bytes, d2h_bytes, kernel_launches, nvlink_bytes, device_mem_used;
+} dfgpu_metrics;
+
+const char *dfgpu_last_error(void);
+const char *dfgpu_version(void);
+
+/* ---- context -------------------------------------------------------------------------- */
+void dfgpu_options_default(dfgpu_options *opts);
+dfgpu_status dfgpu_ctx_create(const dfgpu_options *opts, dfgpu_ctx **out);
+void dfgpu_ctx_destroy(dfgpu_ctx *ctx);
+dfgpu_status dfgpu_ctx_synchronize(dfgpu_ctx *ctx);
+/* raw CUDA stream (cudaStream_t) every operator of this ctx launches on — for CUDA-event timing */
+void *dfgpu_ctx_stream(dfgpu_ctx *ctx);
+/* number of kernels this library launched on ctx so far (bench.py "gpu_launches") */
+int64_t dfgpu_ctx_kernel_launches(const dfgpu_ctx *ctx);
+/* pinned host memory for callers that want PCIe-speed uploads (bench e2e leg) */
+dfgpu_status dfgpu_host_alloc(dfgpu_ctx *ctx, int64_t bytes, void **out);
+void dfgpu_host_free(dfgpu_ctx *ctx, void *p);
+
+/* ---- RecordBatch in HBM (arrow RecordBatch; ownership rules of SURVEY §8b) -------------- */
+/* `array` must be a struct array (one child per column) as produced by
+ * `RecordBatch -> StructArray -> FFI` / pyarrow `RecordBatch._export_to_c`.
+ * buffers_on_device != 0: the ArrowArray's buffer pointers are already device pointers on
+ * opts.device (borrowed until the batch is freed; no copy) — the roofline benches use this. */
+dfgpu_status dfgpu_batch_import(dfgpu_ctx *ctx, const struct ArrowArray *array,
+                                const struct ArrowSchema *schema, int32_t buffers_on_device,
+                                dfgpu_batch **out);
+dfgpu_status dfgpu_batch_export(dfgpu_ctx *ctx, const dfgpu_batch *batch, struct ArrowArray *out_array,
+                                struct ArrowSchema *out_schema);
+int64_t dfgpu_batch_num_rows(const dfgpu_batch *batch);
+int32_t dfgpu_batch_num_columns(const dfgpu_batch *batch);
+dfgpu_status dfgpu_batch_schema(const dfgpu_batch *batch, struct ArrowSchema *out_schema);
+/* compute::concat_batches (hash_join.rs:764) / CoalesceBatchesExec */
+dfgpu_status dfgpu_batch_concat(dfgpu_ctx *ctx, dfgpu_batch *const *batches, int32_t n, dfgpu_batch **out);
+/* zero-copy row slice (RecordBatch::slice; row_hash.rs:478-502 output chunking) */
+dfgpu_status dfgpu_batch_slice(dfgpu_ctx *ctx, const dfgpu_batch *batch, int64_t offset, int64_t length,
+                               dfgpu_batch **out);
+void dfgpu_batch_free(dfgpu_batch *batch);
+
+/* ---- create_hashes (common/src/hash_utils.rs:357-416) — test hook; seed 0 is the fixed
+ * RandomState::with_seeds(0,0,0,0) of joins (hash_join.rs:329) and repartition (repartition/mod.rs:115) */
+dfgpu_status dfgpu_create_hashes(dfgpu_ctx *ctx, const dfgpu_batch *batch, const int32_t *cols, int32_t n_cols,
+                                 uint64_t seed, uint64_t *host_out);
+
+/* ---- AggregateExec / GroupedHashAggregateStream (aggregates/mod.rs:242-299, row_hash.rs) --- */
+typedef struct dfgpu_agg_desc {
+    int32_t func;       /* DFGPU_SUM ...                                                       */
+    const char *name;   /* display name, e.g. "SUM(l_quantity)"; state fields become name[sum] */
+    int32_t arg_col;    /* first-stage modes: input column of the argument, -1 = COUNT(*)/COUNT(1)
+                           final modes: ignored — state columns are resolved by position,
+                           group_cols + running offset (aggregates/mod.rs:1038-1067)           */
+    int32_t filter_col; /* Boolean FILTER column or -1 (first-stage modes only)                */
+} dfgpu_agg_desc;
+
+/* input_schema: schema of the batches that will be pushed (raw rows, or the Partial output
+ * schema in Final modes).  group_cols: indices of the group-by columns (Final modes: 0..n-1). */
+dfgpu_status dfgpu_agg_create(dfgpu_ctx *ctx, int32_t mode, const struct ArrowSchema *input_schema,
+                              const int32_t *group_cols, int32_t n_group_cols, const dfgpu_agg_desc *aggs,
+                              int32_t n_aggs, dfgpu_agg **out);
+/* create_schema (aggregates/mod.rs:749-787): keys ++ state fields (Partial) | result fields */
+dfgpu_status dfgpu_agg_output_schema(const dfgpu_agg *agg, struct ArrowSchema *out_schema);
+/* group_aggregate_batch (row_hash.rs:524-613): GroupValues::intern + update_batch/merge_batch */
+dfgpu_status dfgpu_agg_push(dfgpu_agg *agg, const dfgpu_batch *batch);
+dfgpu_status dfgpu_agg_push_arrow(dfgpu_agg *agg, const struct ArrowArray *batch);
+dfgpu_status dfgpu_agg_num_groups(dfgpu_agg *agg, int64_t *out);
+/* emit(EmitTo::All) (row_hash.rs:626-662); resets the operator like the reference's
+ * early emit (row_hash.rs:723-734) so it can be called mid-stream in Partial mode. */
+dfgpu_status dfgpu_agg_emit(dfgpu_agg *agg, dfgpu_batch **out);
+dfgpu_status dfgpu_agg_emit_arrow(dfgpu_agg *agg, struct ArrowArray *out_array, struct ArrowSchema *out_schema);
+dfgpu_status dfgpu_agg_metrics(const dfgpu_agg *agg, dfgpu_metrics *out);
+void dfgpu_agg_destroy(dfgpu_agg *agg);
+
+/* ---- HashJoinExec (joins/hash_join.rs:272-356, 505-674); left = build, right = probe ------ */
+dfgpu_status dfgpu_join_create(dfgpu_ctx *ctx, int32_t join_type, int32_t partition_mode, int32_t null_equals_null,
+                               const struct ArrowSchema *build_schema, const struct ArrowSchema *probe_schema,
+                               const int32_t *build_keys, const int32_t *probe_keys, int32_t n_keys,
+                               dfgpu_join **out);
+/* build_join_schema (joins/utils.rs:657-729) */
+dfgpu_status dfgpu_join_output_schema(const dfgpu_join *join, struct ArrowSchema *out_schema);
+/* collect_left_input (hash_join.rs:678-768): push all build batches, then finish */
+dfgpu_status dfgpu_join_build_push(dfgpu_join *join, const dfgpu_batch *batch);
+dfgpu_status dfgpu_join_build_finish(dfgpu_join *join);
+/* process_probe_batch (hash_join.rs:1238-1343).  After build_finish the table is read-only;
+ * the visited bitmap is updated with atomics.  Output holds every row the reference emits
+ * for this probe batch (all its <=batch_size sub-batches concatenated). */
+dfgpu_status dfgpu_join_probe(dfgpu_join *join, const dfgpu_batch *probe, dfgpu_batch **out);
+/* process_unmatched_build_batch (hash_join.rs:1348-1388); *out = NULL when the join type
+ * produces nothing at the end (Inner, Right, RightSemi, RightAnti). */
+dfgpu_status dfgpu_join_emit_unmatched(dfgpu_join *join, dfgpu_batch **out);
+dfgpu_status dfgpu_join_metrics(const dfgpu_join *join, dfgpu_metrics *out);
+void dfgpu_join_destroy(dfgpu_join *join);
+
+/* ---- RepartitionExec(Hash) / BatchPartitioner (repartition/mod.rs:133-217, 442-580) -------- */
+/* out_parts[n_parts]; entries for empty partitions are NULL (empty batches are never sent,
+ * repartition/mod.rs:196-214).  Row order inside a partition follows input order. */
+dfgpu_status dfgpu_partition_hash(dfgpu_ctx *ctx, const dfgpu_batch *batch, const int32_t *key_cols,
+                                  int32_t n_keys, int32_t n_parts, dfgpu_batch **out_parts);
+/* The exchange itself: parts[world] (NULL = nothing for that rank) -> concatenation of what
+ * every rank sent to this rank.  NCCL all-to-all over NVLink; world == 1 degenerates to a move.
+ * *out may be NULL when nothing was received.  `schema` describes the batches (needed when all
+ * of this rank's parts are NULL). */
+dfgpu_status dfgpu_exchange_all_to_all(dfgpu_ctx *ctx, dfgpu_batch *const *parts, const struct ArrowSchema *schema,
+                                       dfgpu_batch **out);
+/* 128-byte ncclUniqueId for dfgpu_options.nccl_unique_id: rank 0 creates it and shares it with
+ * the other ranks out of band (the reference has no analogue: its exchange is in-process). */
+dfgpu_status dfgpu_nccl_get_unique_id(void *out128);
+/* CollectLeft build-side replication (hash_join.rs:594-606): all-gather of a batch */
+dfgpu_status dfgpu_exchange_all_gather(dfgpu_ctx *ctx, const dfgpu_batch *local, const struct ArrowSchema *schema,
+                                       dfgpu_batch **out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DFGPU_H */

@@ -1,0 +1,137 @@
+"""-m gpu parity tests for the hash join: CUDA path vs the reference's golden tables
+(tests/golden/hash_join.json, from hash_join.rs:1553-2943) and vs the CPU oracle (differential,
+like core/tests/fuzz_cases/join_fuzz.rs).  Outputs are compared as sorted multisets of rows."""
+import json
+import os
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+import oracle
+from gpu_helpers import gpu_ctx, random_keys
+from util import assert_rows_equal, rows_of
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+JOINS = json.load(open(os.path.join(G, "hash_join.json")))
+JT = {"Inner": "inner", "Left": "left", "Right": "right", "Full": "full", "LeftSemi": "left_semi",
+      "RightSemi": "right_semi", "LeftAnti": "left_anti", "RightAnti": "right_anti"}
+ALL_TYPES = list(oracle.JOIN_TYPES)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = gpu_ctx()
+    yield c
+    c.close()
+
+
+def gpu_join(ctx, jt, left, right, on, null_equals_null=False, left_schema=None, right_schema=None):
+    import datafusion_upstream_b200 as df
+    ls = left_schema or left[0].schema
+    rs = right_schema or right[0].schema
+    j = df.GpuHashJoinExec(ctx, ls, rs, on, df.JoinType(oracle.JOIN_TYPES[jt]), df.PartitionMode.CollectLeft, null_equals_null)
+    out = j.execute(left, right)
+    names = j.schema.names
+    j.close()
+    return out, names
+
+
+def batches(side):
+    return [pa.record_batch([pa.array(c, pa.int32()) for c in b["columns"]], names=b["names"]) for b in side["batches"]]
+
+
+@pytest.mark.parametrize("case", JOINS, ids=[c["name"] for c in JOINS])
+def test_join_golden(ctx, case):
+    left, right = batches(case["left"]), batches(case["right"])
+    on = [(left[0].schema.names.index(l), right[0].schema.names.index(r)) for l, r in case["on"]]
+    c = gpu_ctx(force_hash_collisions=True) if case.get("force_collisions") else ctx
+    out, names = gpu_join(c, JT[case["join_type"]], left, right, on)
+    assert names == case["expected_header"]
+    assert_rows_equal(rows_of(out), [tuple(r) for r in case["expected"]], what=case["name"])
+
+
+def rand_side(rng, n, key_kinds, card, nulls, tag):
+    cols = [random_keys(rng, n, k, card, nulls) for k in key_kinds]
+    cols.append(pa.array(np.arange(n) + (1000000 if tag == "r" else 0), pa.int64()))
+    cols.append(pa.array([f"{tag}{i % 13}" if i % 7 else None for i in range(n)], pa.string()))
+    return pa.record_batch(cols, names=[f"{tag}k{i}" for i in range(len(key_kinds))] + [tag + "id", tag + "s"])
+
+
+KEYS = [["int64"], ["int32", "int32"], ["utf8"], ["utf8", "int16"], ["date32"], ["decimal"], ["int64", "date32", "int32"], ["bool", "uint8"]]
+
+
+@pytest.mark.parametrize("jt", ALL_TYPES)
+@pytest.mark.parametrize("keys", KEYS, ids=lambda k: "+".join(k))
+def test_join_fuzz_vs_oracle(ctx, jt, keys):
+    rng = np.random.default_rng(sum(map(ord, jt + "".join(keys))))
+    left = [rand_side(rng, n, keys, 60, 0.1, "l") for n in (150, 1, 90)]
+    right = [rand_side(rng, n, keys, 75, 0.1, "r") for n in (400, 0, 333)]
+    on = [(i, i) for i in range(len(keys))]
+    out, _ = gpu_join(ctx, jt, left, right, on)
+    want = oracle.hash_join(jt, left, right, on)
+    assert_rows_equal(rows_of(out), rows_of(want), what=f"{jt} {keys}")
+
+
+@pytest.mark.parametrize("jt", ALL_TYPES)
+def test_join_null_equals_null(ctx, jt):
+    """INTERSECT/EXCEPT plans join with null_equals_null (hash_join.rs:1067-1076)."""
+    rng = np.random.default_rng(4)
+    left = [rand_side(rng, 120, ["int32", "utf8"], 12, 0.3, "l")]
+    right = [rand_side(rng, 200, ["int32", "utf8"], 14, 0.3, "r")]
+    on = [(0, 0), (1, 1)]
+    out, _ = gpu_join(ctx, jt, left, right, on, null_equals_null=True)
+    want = oracle.hash_join(jt, left, right, on, null_equals_null=True)
+    assert_rows_equal(rows_of(out), rows_of(want), what=jt)
+
+
+@pytest.mark.parametrize("jt", ALL_TYPES)
+def test_join_empty_sides(ctx, jt):
+    rng = np.random.default_rng(2)
+    l, r = rand_side(rng, 50, ["int64"], 10, 0.0, "l"), rand_side(rng, 70, ["int64"], 10, 0.0, "r")
+    for left, right in (([l.slice(0, 0)], [r]), ([l], [r.slice(0, 0)]), ([l.slice(0, 0)], [r.slice(0, 0)])):
+        out, _ = gpu_join(ctx, jt, left, right, [(0, 0)])
+        want = oracle.hash_join(jt, left, right, [(0, 0)])
+        assert_rows_equal(rows_of(out), rows_of(want), what=jt)
+
+
+def test_join_dictionary_keys(ctx):
+    rng = np.random.default_rng(8)
+    lk = random_keys(rng, 300, "dict_utf8", 40, 0.1)
+    rk = random_keys(rng, 500, "utf8", 55, 0.1)
+    left = [pa.record_batch([lk, pa.array(np.arange(300))], names=["k", "l"])]
+    right = [pa.record_batch([rk.dictionary_encode(), pa.array(np.arange(500))], names=["k", "r"])]
+    for jt in ("inner", "full", "left_anti"):
+        out, _ = gpu_join(ctx, jt, left, right, [(0, 0)])
+        want = oracle.hash_join(jt, left, right, [(0, 0)])
+        assert_rows_equal(rows_of(out), rows_of(want), what=jt)
+
+
+def test_join_q3_shape_large(ctx):
+    """Q3 shape (config C3) at a size the oracle finishes in seconds: PK-FK joins, duplicates on the probe
+    side, multi-chunk probe; plus a size-independent property (every probe row with an existing key appears)."""
+    rng = np.random.default_rng(6)
+    nb, np_ = 200_000, 1_500_000
+    okey = rng.permutation(nb * 4)[:nb].astype(np.int64)
+    orders = pa.record_batch([pa.array(okey), pa.array(rng.integers(8000, 10000, nb).astype(np.int32), pa.int32()).cast(pa.date32()),
+                              pa.array(np.zeros(nb, np.int32))], names=["o_orderkey", "o_orderdate", "o_shippriority"])
+    lkey = rng.integers(0, nb * 4, np_).astype(np.int64)
+    line = pa.record_batch([pa.array(lkey), pa.array(rng.integers(0, 10**7, np_), pa.int64())], names=["l_orderkey", "l_price"])
+    out, _ = gpu_join(ctx, "inner", [orders], [line.slice(0, 700_000), line.slice(700_000)], [(0, 0)])
+    got = pa.Table.from_batches(out)
+    want = oracle.hash_join("inner", [orders], [line], [(0, 0)])
+    assert got.num_rows == want.num_rows == int(np.isin(lkey, okey).sum())
+    assert_rows_equal(rows_of(got), rows_of(want))
+
+
+def test_join_errors(ctx):
+    import datafusion_upstream_b200 as df
+    l = pa.record_batch([pa.array([1], pa.int64())], names=["a"])
+    r = pa.record_batch([pa.array(["x"])], names=["a"])
+    with pytest.raises(df.DfGpuError) as e:
+        gpu_join(ctx, "inner", [l], [r], [(0, 0)])
+    assert e.value.kind == "Plan"
+    with pytest.raises(df.DfGpuError) as e:
+        gpu_join(ctx, "inner", [l], [l], [])
+    assert e.value.kind == "Plan" and "non-empty" in str(e.value)
