@@ -78,7 +78,8 @@ __device__ __forceinline__ void apply_global(const OpDesc &op, uint32_t g, uint6
     case OP_MAX_F64: { double d = __longlong_as_double((long long)lo); if (d == d) atomicMax((unsigned long long *)st, (unsigned long long)f64_to_ordered(d)); break; }
     case OP_MIN_I128: case OP_MAX_I128: {
         u128_t v{lo, hi};
-        u128_t cur{((volatile uint64_t *)st)[0], ((volatile uint64_t *)st)[1]};
+        u128_t cur{0, 0};
+        atomic_cas128(st, cur, cur);  // atomic 128-bit read (two 64-bit loads could tear)
         for (;;) {
             bool better = op.kind == OP_MIN_I128 ? lt128_signed(v, cur) : lt128_signed(cur, v);
             if (!better) break;
@@ -151,6 +152,7 @@ __global__ void __launch_bounds__(ACC_T) k_accumulate(const OpDesc *__restrict__
                 if (PRIVATE) {
                     uint64_t *rec = &sm[((uint64_t)g[k] * wpg + op.woff) * ACC_T + tid];
                     uint64_t a = rec[0], b = op.nwords == 2 ? rec[ACC_T] : 0;
+                    if (op.seen_bit >= 0) sm[((uint64_t)g[k] * wpg + wpg - 1) * ACC_T + tid] |= 1ULL << op.seen_bit;
                     if ((op.kind == OP_MIN_F64 || op.kind == OP_MAX_F64)) {
                         double d = __longlong_as_double((long long)lo[k]);
                         if (!(d == d)) continue;  // NaN never replaces (strict compare is false)
@@ -158,7 +160,6 @@ __global__ void __launch_bounds__(ACC_T) k_accumulate(const OpDesc *__restrict__
                     combine_raw(op.kind, a, b, lo[k], hi[k]);
                     rec[0] = a;
                     if (op.nwords == 2) rec[ACC_T] = b;
-                    if (op.seen_bit >= 0) sm[((uint64_t)g[k] * wpg + wpg - 1) * ACC_T + tid] |= 1ULL << op.seen_bit;
                 } else {
                     apply_global(op, g[k], lo[k], hi[k]);
                     if (op.seen) op.seen[g[k]] = 1;

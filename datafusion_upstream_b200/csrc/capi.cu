@@ -47,6 +47,14 @@ __global__ void k_create_hashes(HashCols hc, uint64_t seed, int force_collisions
         out[i] = h;
     }
 }
+void ctx_release(Ctx *c) {
+    if (c->refs.fetch_sub(1) != 1) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    ctx_destroy_nccl(c);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
 void create_hashes_device(Ctx *ctx, const std::vector<const DevCol *> &cols, int64_t row_off, int64_t n, uint64_t seed, uint64_t *out) {
     if ((int)cols.size() > MAX_KEY_COLS) fail(DFGPU_NOT_IMPLEMENTED, "more than 16 hash columns");
     HashCols hc;
@@ -129,12 +137,7 @@ dfgpu_status dfgpu_ctx_create(const dfgpu_options *opts, dfgpu_ctx **out) {
     DF_CATCH
 }
 void dfgpu_ctx_destroy(dfgpu_ctx *ctx) {
-    if (!ctx) return;
-    cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
-    ctx_destroy_nccl(ctx);
-    cudaStreamDestroy(ctx->stream);
-    delete ctx;
+    if (ctx) dfgpu::ctx_release(ctx);  // torn down once the last batch / operator on it is gone
 }
 dfgpu_status dfgpu_ctx_synchronize(dfgpu_ctx *ctx) {
     DF_TRY

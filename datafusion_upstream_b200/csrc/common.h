@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -106,10 +107,29 @@ struct dfgpu_ctx {
     void *nccl_comm = nullptr;  // ncclComm_t
     dfgpu::PinnedPool pinned;
     uint64_t *flush_dummy = nullptr;
+    std::atomic<int> refs{1};  // the creator's handle + every batch / operator created on this ctx
 };
 
 namespace dfgpu {
 typedef dfgpu_ctx Ctx;
+void ctx_release(Ctx *c);  // drops one reference; tears the context down with the last one
+// Reference-counted context pointer: handles may be destroyed in any order by the host language
+// (garbage collectors, Rust drop order) without dangling.
+struct CtxHold {
+    Ctx *c = nullptr;
+    CtxHold() {}
+    CtxHold(const CtxHold &o) : c(o.c) { if (c) c->refs.fetch_add(1); }
+    CtxHold &operator=(const CtxHold &o) { return *this = o.c; }
+    CtxHold &operator=(Ctx *n) {
+        if (n) n->refs.fetch_add(1);
+        if (c) ctx_release(c);
+        c = n;
+        return *this;
+    }
+    ~CtxHold() { if (c) ctx_release(c); }
+    operator Ctx *() const { return c; }
+    Ctx *operator->() const { return c; }
+};
 
 // device buffer allocated from the stream-ordered pool of ctx->stream
 struct DevBuf {
@@ -161,7 +181,7 @@ typedef std::shared_ptr<DevCol> ColRef;
 }  // namespace dfgpu
 
 struct dfgpu_batch {
-    dfgpu::Ctx *ctx = nullptr;
+    dfgpu::CtxHold ctx;
     int64_t num_rows = 0;
     std::vector<dfgpu::ColRef> cols;
     dfgpu::Schema schema() const {

@@ -197,9 +197,16 @@ __global__ void __launch_bounds__(256) k_intern_rows(TableView t, const uint8_t 
                         eq = words_equal(kp, packed + j * W, W);
                     }
                 } else if (VAR) {
-                    eq = t.glen[pl] == (int32_t)klen && bytes_equal(kp, t.heap + t.goff[pl], klen);
+                    // the key store is written by other SMs during this kernel: bypass the (non-coherent) L1
+                    eq = __ldcg(&t.glen[pl]) == (int32_t)klen;
+                    if (eq) {
+                        const uint8_t *sp = t.heap + __ldcg(&t.goff[pl]);
+                        for (int64_t k = 0; k < klen && eq; k++) eq = __ldcg(sp + k) == kp[k];
+                    }
                 } else {
-                    eq = words_equal(kp, t.grows + (uint64_t)pl * W, W);
+                    const uint8_t *sp = t.grows + (uint64_t)pl * W;
+                    eq = true;
+                    for (int k = 0; k < W && eq; k += 8) eq = __ldcg((const uint64_t *)(sp + k)) == *(const uint64_t *)(kp + k);
                 }
                 if (eq) { res = (pl & GID_PENDING) ? (GID_PENDING | (uint32_t)s) : pl; break; }
             }
@@ -254,12 +261,13 @@ __global__ void __launch_bounds__(256) k_pack_keys(PackPlan p, int64_t n, uint8_
     for (; i < n; i += stride) {
         uint8_t *row = out + i * p.W;
         for (int k = 0; k < p.W; k += 8) *(uint64_t *)(row + k) = 0;
-        bool any_null = false;
+        bool any_null = false, miss = false;
         for (int c = 0; c < p.ncols; c++) {
             const PackCol &pc = p.c[c];
             if (pc.kind == 2) {
                 uint32_t id = pc.ids[i];
-                if (id == GID_NONE) any_null = true;
+                if (id == GID_NONE) miss = true;            // find-only: string absent from the table
+                else if (id == STRID_NULL) any_null = true;  // NULL is encoded in the id field itself
                 *(uint32_t *)(row + pc.off) = id;
                 continue;
             }
@@ -284,7 +292,7 @@ __global__ void __launch_bounds__(256) k_pack_keys(PackPlan p, int64_t n, uint8_
                 row[pc.off] = ((const uint8_t *)pc.v.values)[i];
             }
         }
-        if (excl) excl[i] = (null_policy == NULLS_EXCLUDED && any_null) ? 1 : 0;
+        if (excl) excl[i] = (miss || (null_policy == NULLS_EXCLUDED && any_null)) ? 1 : 0;
     }
 }
 

@@ -16,7 +16,7 @@
 #include "groups.h"
 
 struct dfgpu_join {
-    dfgpu::Ctx *ctx = nullptr;
+    dfgpu::CtxHold ctx;
     int join_type = 0, partition_mode = 0;
     bool null_equals_null = false;
     dfgpu::Schema build_schema, probe_schema, out_schema;

@@ -18,8 +18,10 @@ def gpu_agg(ctx, mode, batches, group_by, specs, schema=None):
     """specs: list of (func, arg column name | None, display name, filter column name | None)."""
     import datafusion_upstream_b200 as df
     schema = schema or batches[0].schema
-    exprs = [df.AggregateExpr(df.AggFunc(FUNCS[f]), a, n, flt) for f, a, n, flt in specs]
     modes = {"partial": 0, "final": 1, "final_partitioned": 2, "single": 3, "single_partitioned": 4}
+    if mode.startswith("final"):   # state columns are resolved by position (aggregates/mod.rs:1038-1067)
+        specs = [(f, None, n, None) for f, _, n, _ in specs]
+    exprs = [df.AggregateExpr(df.AggFunc(FUNCS[f]), a, n, flt) for f, a, n, flt in specs]
     op = df.GpuAggregateExec(ctx, df.AggregateMode(modes[mode]), schema, group_by, exprs)
     for b in batches:
         op.push(b)
@@ -84,7 +86,8 @@ def random_keys(rng, n, kind, card, null_frac=0.0):
     """Key arrays of many Arrow types with `card` distinct values."""
     base = rng.integers(0, card, n)
     if kind == "int64":
-        vals = (base.astype(np.int64) * 0x9E3779B97F4A7C15 % (1 << 63)).astype(np.int64) - (base % 3 == 0) * 7
+        with np.errstate(over="ignore"):
+            vals = (base.astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15)).view(np.int64) - (base % 3 == 0) * 7
         arr = pa.array(vals, pa.int64())
     elif kind == "int64_small":
         arr = pa.array(base.astype(np.int64) - 1, pa.int64())   # includes -1 == the U64 EMPTY bit pattern
