@@ -1,0 +1,422 @@
+#!/usr/bin/env python3
+"""Headline benchmark for the hash-table operator path (BASELINE.json).
+
+A "step" is one pass of the hot path over one batch of synthetic input.  Default workload at N=1
+is configs[1]: ClickBench-shaped `SELECT UserID, COUNT(*) ... GROUP BY UserID` over 100 M synthetic
+Int64 keys (~17 M groups) on one B200.  Other workloads (`--workload q1|join`) are the Q1-/Q3-shaped
+configurations and are reported the same way.
+
+    python bench.py --gpus N --steps K --warmup W [--workload c2|q1|join] [--impl reference]
+
+Prints ONE JSON line (rank 0).  `value` = whole-job input rows/s with inputs resident in HBM;
+`e2e` = the same metric through the C-ABI with HOST (pinned) Arrow buffers, H2D/D2H inside the
+timed region; `roofline` = dominant kernel, CUDA-event timed live on the launching stream;
+`cpu_baseline` = the CPU oracle (port of the reference operators) on the box's host cores.
+"""
+import argparse
+import ctypes
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import pyarrow as pa  # noqa: E402
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic data (deterministic, generated on the device with torch; seed 42 + rank)
+# ------------------------------------------------------------------------------------------------
+def _mix64_torch(x):
+    import torch
+    m = (1 << 63) - 1
+
+    def lsr(v, k):  # logical shift right on int64
+        return (v >> k) & ((1 << (64 - k)) - 1)
+    x = x ^ lsr(x, 30)
+    x = x * torch.tensor(-4658895280553007687, dtype=torch.int64, device=x.device)   # 0xbf58476d1ce4e5b9
+    x = x ^ lsr(x, 27)
+    x = x * torch.tensor(-7723592293110705685, dtype=torch.int64, device=x.device)   # 0x94d049bb133111eb
+    x = x ^ lsr(x, 31)
+    _ = m
+    return x
+
+
+def gen_c2_keys(n, seed, device, universe=40_000_000):
+    """Zipf(s~1) ranks (log-uniform inverse CDF) over `universe` ids, mapped through a 64-bit bijective
+    mixer so keys are sparse 64-bit values like real UserIDs."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    out = torch.empty(n, dtype=torch.int64, device=device)
+    step = 1 << 24
+    for o in range(0, n, step):
+        m = min(step, n - o)
+        u = torch.rand(m, generator=g, device=device, dtype=torch.float64)
+        rank = torch.exp(u * math.log(universe)).to(torch.int64)
+        out[o:o + m] = _mix64_torch(rank)
+    return out
+
+
+def gen_q1(n, seed, device):
+    """lineitem-shaped columns: 2 key columns with the TPC-H joint distribution, 5 Decimal128 columns."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    pick = torch.multinomial(torch.tensor([0.25, 0.006, 0.493, 0.251], device=device), n, replacement=True, generator=g)
+    flag = torch.tensor([65, 78, 78, 82], dtype=torch.uint8, device=device)[pick]      # A N N R
+    status = torch.tensor([70, 70, 79, 70], dtype=torch.uint8, device=device)[pick]    # F F O F
+
+    def dec(lo, hi):  # int64 -> sign-extended 128-bit little endian pairs
+        v = torch.randint(lo, hi, (n,), generator=g, device=device, dtype=torch.int64)
+        return torch.stack([v, v >> 63], dim=1).contiguous()
+    cols = {"qty": dec(100, 5001), "price": dec(90000, 10495001), "disc": dec(0, 11),
+            "disc_price": dec(10**9, 10**11), "charge": dec(10**11, 10**13)}
+    return flag, status, cols
+
+
+class Clocks:
+    """nvidia-smi clock / throttle sampling DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, dev):
+        self.dev, self.p = dev, None
+
+    def __enter__(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(self.dev)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+        return self
+
+    def __exit__(self, *a):
+        self.result = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if not self.p:
+            return
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except Exception:
+            return
+        sm, mx, reasons = [], [], set()
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if sm:
+            self.result = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# workloads
+# ------------------------------------------------------------------------------------------------
+def build_workload(args, df, ctx, torch, device, rank):
+    """Returns dict(schema, dev_batch, host_batch_factory, make_op, rows, algo_bytes_fn, name, cpu)."""
+    import oracle
+    w = {}
+    n = args.rows
+    if args.workload == "c2":
+        keys = gen_c2_keys(n, 42 + rank, device)
+        schema = pa.schema([("UserID", pa.int64())])
+        w["name"] = f"ClickBench-shaped GROUP BY UserID COUNT(*), {n} Int64 rows, Zipf(1.0) over 40M ids (BASELINE configs[1])"
+        w["dev"] = df.DeviceBatch.from_device(ctx, schema, [{"buffers": [None, keys.data_ptr()], "null_count": 0}], n, keep=keys)
+        w["schema"] = schema
+        w["group_by"] = ["UserID"]
+        w["exprs"] = [df.AggregateExpr(df.AggFunc.Count, None, "COUNT(*)")]
+        w["in_bytes"] = 8 * n
+        w["out_row_bytes"] = 16
+        host_cols = [("UserID", pa.int64(), keys)]
+        w["cpu"] = lambda threads, sample: oracle.bench_groupby_count_i64(keys[:sample].cpu().numpy(), threads)
+    elif args.workload == "q1":
+        flag, status, cols = gen_q1(n, 42 + rank, device)
+        d152, d384, d386 = pa.decimal128(15, 2), pa.decimal128(38, 4), pa.decimal128(38, 6)
+        schema = pa.schema([("l_returnflag", pa.uint8()), ("l_linestatus", pa.uint8()), ("l_quantity", d152), ("l_extendedprice", d152),
+                            ("l_discount", d152), ("disc_price", d384), ("charge", d386)])
+        w["name"] = f"TPC-H Q1-shaped aggregation, {n} rows, 4 groups, 2xUInt8 keys, Decimal128 SUMx4 AVGx3 COUNT(*) (82 B/row variant of configs[0])"
+        order = ["qty", "price", "disc", "disc_price", "charge"]
+        bufs = [{"buffers": [None, flag.data_ptr()]}, {"buffers": [None, status.data_ptr()]}] + [{"buffers": [None, cols[c].data_ptr()]} for c in order]
+        w["dev"] = df.DeviceBatch.from_device(ctx, schema, bufs, n, keep=(flag, status, cols))
+        w["schema"] = schema
+        w["group_by"] = ["l_returnflag", "l_linestatus"]
+        A = df.AggregateExpr
+        w["exprs"] = [A(df.AggFunc.Sum, "l_quantity", "sum_qty"), A(df.AggFunc.Sum, "l_extendedprice", "sum_base_price"),
+                      A(df.AggFunc.Sum, "disc_price", "sum_disc_price"), A(df.AggFunc.Sum, "charge", "sum_charge"),
+                      A(df.AggFunc.Avg, "l_quantity", "avg_qty"), A(df.AggFunc.Avg, "l_extendedprice", "avg_price"),
+                      A(df.AggFunc.Avg, "l_discount", "avg_disc"), A(df.AggFunc.Count, None, "count_order")]
+        w["in_bytes"] = 82 * n
+        w["out_row_bytes"] = 0
+        host_cols = [("l_returnflag", pa.uint8(), flag), ("l_linestatus", pa.uint8(), status)] + \
+                    [(nm, t, cols[c]) for (nm, t), c in zip(list(zip(schema.names, schema.types))[2:], order)]
+
+        def cpu(threads, sample):
+            f, s = flag[:sample].cpu().numpy(), status[:sample].cpu().numpy()
+            d = [cols[c][:sample].cpu().numpy() for c in ("qty", "price", "disc_price", "charge", "disc")]
+            return oracle.bench_q1(f, s, d, threads)
+        w["cpu"] = cpu
+    else:
+        raise SystemExit(f"unknown workload {args.workload}")
+    w["host_cols"] = host_cols
+    return w
+
+
+def pinned_batch(ctx, schema, host_cols, n, torch):
+    """Arrow RecordBatch whose buffers live in pinned host memory (PCIe-speed H2D for the e2e leg)."""
+    arrays, keep, nbytes = [], [], 0
+    for name, typ, t in host_cols:
+        src = t.contiguous().cpu().numpy().reshape(-1).view(np.uint8)
+        ptr = ctx.host_alloc(src.nbytes)
+        ctypes.memmove(ptr, src.ctypes.data, src.nbytes)
+        buf = pa.foreign_buffer(ptr, src.nbytes)
+        arrays.append(pa.Array.from_buffers(typ, n, [None, buf]))
+        keep.append(ptr)
+        nbytes += src.nbytes
+    return pa.RecordBatch.from_arrays(arrays, schema=schema), keep, nbytes
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import datafusion_upstream_b200 as df
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group(backend="gloo")     # bootstrap / barrier only; the data path uses NCCL inside libdfgpu
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    uid = None
+    if world > 1:
+        box = [df.GpuContext.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        uid = box[0]
+    ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+    w = build_workload(args, df, ctx, torch, device, rank)
+    n = args.rows
+    torch.cuda.synchronize()
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    hold = []
+
+    def step_device():
+        """One pass of the hot path, inputs resident in HBM, result left in HBM."""
+        if world == 1:
+            op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
+            op.push(w["dev"])
+            out = op.emit_device()
+            hold.append((op, out))
+            return out
+        # Partial -> hash repartition (NCCL all-to-all over NVLink) -> FinalPartitioned
+        part = df.GpuAggregateExec(ctx, df.AggregateMode.Partial, w["schema"], w["group_by"], w["exprs"])
+        part.push(w["dev"])
+        st = part.emit_device()
+        rp = df.GpuRepartitionExec(ctx, part.schema, list(range(len(w["group_by"]))), world)
+        recv = rp.exchange(rp.partition_device(st))
+        fin = df.GpuAggregateExec(ctx, df.AggregateMode.FinalPartitioned, part.schema, list(range(len(w["group_by"]))),
+                                  [df.AggregateExpr(e.func, None, e.name) for e in w["exprs"]])
+        if recv is not None:
+            fin.push(recv)
+        out = fin.emit_device()
+        hold.append((part, st, recv, fin, out))
+        return out
+
+    for _ in range(args.warmup):
+        out = step_device()
+        groups = out.num_rows
+        hold.clear()
+    barrier()
+    ctx.set_profiling(True)
+    launches0 = ctx.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with Clocks(local) as clk:
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            out = step_device()
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    groups = out.num_rows
+    launches = ctx.kernel_launches - launches0
+    prof = ctx.profile()
+    ctx.set_profiling(False)
+    hold.clear()
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        gt = torch.tensor([groups], dtype=torch.int64)
+        dist.all_reduce(gt)
+        groups = int(gt[0])
+    ms_per_step = ms / args.steps
+    value = n * world / (ms_per_step / 1e3)
+
+    # ---- e2e: host (pinned) Arrow buffers through the C-ABI, H2D + D2H inside the timed region ----
+    e2e = None
+    if world == 1 and not args.no_e2e:
+        hb, keep, h2d = pinned_batch(ctx, w["schema"], w["host_cols"], n, torch)
+        e2e_steps = max(1, min(args.steps, 5))
+
+        def step_host():
+            op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
+            op.push(hb)
+            res = op.emit()         # D2H into pinned buffers + Arrow import
+            op.close()
+            return res
+        step_host()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            res = step_host()
+        barrier()
+        dt = (time.perf_counter() - t0) / e2e_steps
+        e2e = {"value": n / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(res.nbytes), "ms_per_step": dt * 1e3}
+        del hb
+        for p in keep:
+            ctx.host_free(p)
+
+    # ---- roofline of the dominant kernel (CUDA events recorded live by the library) ----
+    peak, peak_src = peaks()
+    roof = None
+    if prof:
+        top = max(prof, key=lambda r: r["ms"])
+        per_launch_ms = top["ms"] / top["launches"]
+        achieved = top["algo_bytes"] / top["launches"] / (per_launch_ms * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(args.workload, {}).get(top["name"])
+        roof = {"bound": "hbm", "kernel": top["name"], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                "launches_per_step": top["launches"] / args.steps, "ms_per_launch": round(per_launch_ms, 4),
+                "kernel_share_of_step": round(top["ms"] / ms, 3),
+                "kernels": {r["name"]: round(r["ms"] / args.steps, 4) for r in prof}}
+    algo_bytes = w["in_bytes"] + w["out_row_bytes"] * (groups // world)
+    # ---- CPU baseline (the oracle port, reference-shaped parallel plan) on rank 0 ----
+    cpu = None
+    if rank == 0 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        sample = min(n, args.cpu_sample)
+        secs, g, _ = w["cpu"](threads, sample)
+        cpu = {"value": sample / secs, "unit": "rows/s", "cores": threads, "kind": "port",
+               "sample": f"first {sample} rows of the same workload, P={threads} Partial -> hash repartition -> FinalPartitioned, 8192-row batches"}
+    if rank == 0:
+        line = {
+            "metric": "input rows/s (hash aggregation, device-resident input) and HBM GB/s", "value": value, "unit": "rows/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int64" if args.workload == "c2" else "i128", "data": "synthetic",
+            "config": {"workload": w["name"], "rows_per_gpu": n, "groups": groups, "l2_policy": "inputs larger than L2 (no flush needed)"
+                       if w["in_bytes"] > 256e6 else "inputs smaller than L2: table/state reset each step", "mode": "Single" if world == 1 else
+                       f"Partial -> NCCL all-to-all -> FinalPartitioned (dp{world})"},
+            "algorithmic_GBps": algo_bytes * world / (ms_per_step * 1e-3) / 1e9,
+            "algorithmic_frac_of_peak": algo_bytes / (ms_per_step * 1e-3) / 1e9 / peak,
+            "clocks": clk.result, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """The reference's own CPU implementation of the path, on the box's host cores.  The reference is
+    Rust and cannot be built here (no cargo/rustc, crates not vendored: DESIGN.md), so this arm times
+    the oracle port in the reference's parallel shape (P x Partial -> hash repartition -> P x Final)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    threads = os.cpu_count() or 1
+    n = min(args.rows, args.cpu_sample)
+    rng = np.random.default_rng(42)
+    if args.workload == "c2":
+        u = rng.random(n)
+        rank_ = np.exp(u * math.log(40_000_000)).astype(np.int64)
+        with np.errstate(over="ignore"):
+            x = rank_.astype(np.uint64)
+            x ^= x >> np.uint64(30); x *= np.uint64(0xbf58476d1ce4e5b9)
+            x ^= x >> np.uint64(27); x *= np.uint64(0x94d049bb133111eb)
+            x ^= x >> np.uint64(31)
+        keys = x.view(np.int64)
+        run = lambda: oracle.bench_groupby_count_i64(keys, threads)
+        name = f"ClickBench-shaped GROUP BY UserID COUNT(*), {args.rows} Int64 rows, Zipf(1.0) over 40M ids (BASELINE configs[1])"
+    else:
+        pick = rng.choice(4, n, p=[0.25, 0.006, 0.493, 0.251])
+        flag = np.array([65, 78, 78, 82], np.uint8)[pick]
+        status = np.array([70, 70, 79, 70], np.uint8)[pick]
+
+        def dec(lo, hi):
+            v = rng.integers(lo, hi, n)
+            return np.stack([v, v >> 63], axis=1).copy()
+        d = [dec(100, 5001), dec(90000, 10495001), dec(10**9, 10**11), dec(10**11, 10**13), dec(0, 11)]
+        run = lambda: oracle.bench_q1(flag, status, d, threads)
+        name = f"TPC-H Q1-shaped aggregation, {args.rows} rows"
+    for _ in range(min(args.warmup, 1)):
+        run()
+    secs = [run()[0] for _ in range(args.steps)]
+    s = statistics.mean(secs)
+    val = n / s
+    sample = f"{n} rows of the workload per step, P={threads} threads, 8192-row batches"
+    print(json.dumps({
+        "impl": "reference", "metric": "input rows/s (hash aggregation, device-resident input) and HBM GB/s", "value": val, "unit": "rows/s",
+        "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup, "ms_per_step": s * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64" if args.workload == "c2" else "i128",
+        "data": "synthetic", "config": {"workload": name},
+        "cpu_baseline": {"value": val, "unit": "rows/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--workload", default="c2", choices=["c2", "q1"])
+    ap.add_argument("--rows", type=int, default=0)
+    ap.add_argument("--cpu-sample", type=int, default=50_000_000)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.rows <= 0:
+        args.rows = 100_000_000 if args.workload == "c2" else 60_012_150
+    if args.warmup < 3 and args.impl != "reference":
+        args.warmup = max(args.warmup, 3)       # timing rules: W >= 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

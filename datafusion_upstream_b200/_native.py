@@ -71,7 +71,7 @@ class Metrics(C.Structure):
 # every symbol include/dfgpu.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "dfgpu_last_error", "dfgpu_version", "dfgpu_options_default", "dfgpu_ctx_create", "dfgpu_ctx_destroy",
-    "dfgpu_ctx_synchronize", "dfgpu_ctx_stream", "dfgpu_ctx_kernel_launches", "dfgpu_host_alloc", "dfgpu_host_free",
+    "dfgpu_ctx_synchronize", "dfgpu_ctx_set_profiling", "dfgpu_ctx_profile_json", "dfgpu_ctx_stream", "dfgpu_ctx_kernel_launches", "dfgpu_host_alloc", "dfgpu_host_free",
     "dfgpu_batch_import", "dfgpu_batch_export", "dfgpu_batch_num_rows", "dfgpu_batch_num_columns", "dfgpu_batch_schema",
     "dfgpu_batch_concat", "dfgpu_batch_slice", "dfgpu_batch_free", "dfgpu_create_hashes", "dfgpu_agg_create",
     "dfgpu_agg_output_schema", "dfgpu_agg_push", "dfgpu_agg_push_arrow", "dfgpu_agg_num_groups", "dfgpu_agg_emit",
@@ -100,6 +100,8 @@ def lib():
     L.dfgpu_ctx_create.argtypes = [C.POINTER(Options), C.POINTER(P)]
     L.dfgpu_ctx_destroy.argtypes = [P]
     L.dfgpu_ctx_synchronize.argtypes = [P]
+    L.dfgpu_ctx_set_profiling.argtypes = [P, C.c_int32]
+    L.dfgpu_ctx_profile_json.argtypes = [P, C.c_char_p, C.c_int64]
     L.dfgpu_ctx_stream.restype = P
     L.dfgpu_ctx_stream.argtypes = [P]
     L.dfgpu_ctx_kernel_launches.restype = C.c_int64

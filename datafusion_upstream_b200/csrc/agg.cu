@@ -10,6 +10,7 @@
 //   GLOBAL   one atomic per (row, state word) into HBM-resident state arrays indexed by group id.
 // Both read each input column once, R rows per thread per op so R independent 128-bit loads are
 // in flight per thread.
+#include <algorithm>
 #include <cfloat>
 #include <chrono>
 

@@ -144,6 +144,40 @@ dfgpu_status dfgpu_ctx_synchronize(dfgpu_ctx *ctx) {
     DF_CUDA(cudaStreamSynchronize(ctx->stream));
     DF_CATCH
 }
+dfgpu_status dfgpu_ctx_set_profiling(dfgpu_ctx *ctx, int32_t enable) {
+    DF_TRY
+    DF_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (auto &r : ctx->prof) { cudaEventDestroy(r.start); cudaEventDestroy(r.stop); }
+    ctx->prof.clear();
+    ctx->profiling = enable != 0;
+    DF_CATCH
+}
+dfgpu_status dfgpu_ctx_profile_json(dfgpu_ctx *ctx, char *buf, int64_t cap) {
+    DF_TRY
+    DF_CUDA(cudaStreamSynchronize(ctx->stream));
+    struct Acc { int64_t launches = 0, bytes = 0; double ms = 0; };
+    std::map<std::string, Acc> by;
+    for (auto &r : ctx->prof) {
+        float ms = 0;
+        DF_CUDA(cudaEventElapsedTime(&ms, r.start, r.stop));
+        Acc &a = by[r.name];
+        a.launches++; a.ms += ms; a.bytes += r.algo_bytes;
+        cudaEventDestroy(r.start); cudaEventDestroy(r.stop);
+    }
+    ctx->prof.clear();
+    std::string s = "[";
+    for (auto &kv : by) {
+        if (s.size() > 1) s += ",";
+        char tmp[256];
+        snprintf(tmp, sizeof tmp, "{\"name\":\"%s\",\"launches\":%lld,\"ms\":%.6f,\"algo_bytes\":%lld}", kv.first.c_str(),
+                 (long long)kv.second.launches, kv.second.ms, (long long)kv.second.bytes);
+        s += tmp;
+    }
+    s += "]";
+    if ((int64_t)s.size() + 1 > cap) fail(DFGPU_INTERNAL, "profile buffer too small");
+    memcpy(buf, s.c_str(), s.size() + 1);
+    DF_CATCH
+}
 void *dfgpu_ctx_stream(dfgpu_ctx *ctx) { return (void *)ctx->stream; }
 int64_t dfgpu_ctx_kernel_launches(const dfgpu_ctx *ctx) { return ctx->launches; }
 dfgpu_status dfgpu_host_alloc(dfgpu_ctx *ctx, int64_t bytes, void **out) {

@@ -108,6 +108,14 @@ struct dfgpu_ctx {
     dfgpu::PinnedPool pinned;
     uint64_t *flush_dummy = nullptr;
     std::atomic<int> refs{1};  // the creator's handle + every batch / operator created on this ctx
+    // optional per-kernel CUDA-event timing (bench.py roofline): name -> (events, launches)
+    bool profiling = false;
+    struct ProfRec {
+        const char *name;
+        cudaEvent_t start, stop;
+        int64_t algo_bytes;
+    };
+    std::vector<ProfRec> prof;
 };
 
 namespace dfgpu {
@@ -129,6 +137,26 @@ struct CtxHold {
     ~CtxHold() { if (c) ctx_release(c); }
     operator Ctx *() const { return c; }
     Ctx *operator->() const { return c; }
+};
+
+// Scoped CUDA-event timer around one kernel launch (active only while ctx->profiling): the events
+// are recorded on the launching stream, so the elapsed time is that kernel's device duration.
+struct KTimer {
+    Ctx *ctx;
+    size_t idx = 0;
+    bool on;
+    KTimer(Ctx *c, const char *name, int64_t algo_bytes = 0) : ctx(c), on(c->profiling) {
+        if (!on) return;
+        dfgpu_ctx::ProfRec r{name, nullptr, nullptr, algo_bytes};
+        cudaEventCreate(&r.start);
+        cudaEventCreate(&r.stop);
+        cudaEventRecord(r.start, c->stream);
+        idx = c->prof.size();
+        c->prof.push_back(r);
+    }
+    ~KTimer() {
+        if (on) cudaEventRecord(ctx->prof[idx].stop, ctx->stream);
+    }
 };
 
 // device buffer allocated from the stream-ordered pool of ctx->stream

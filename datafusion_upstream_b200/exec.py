@@ -87,6 +87,16 @@ class GpuContext:
     def synchronize(self):
         N.check(N.lib().dfgpu_ctx_synchronize(self.h))
 
+    def set_profiling(self, enable: bool):
+        N.check(N.lib().dfgpu_ctx_set_profiling(self.h, int(enable)))
+
+    def profile(self) -> list:
+        """Per-kernel CUDA-event times since the last call: [{name, launches, ms, algo_bytes}]."""
+        import json
+        buf = C.create_string_buffer(1 << 16)
+        N.check(N.lib().dfgpu_ctx_profile_json(self.h, buf, len(buf)))
+        return json.loads(buf.value.decode())
+
     @property
     def stream(self) -> int:
         return N.lib().dfgpu_ctx_stream(self.h)

@@ -94,6 +94,11 @@ void dfgpu_ctx_destroy(dfgpu_ctx *ctx);
 dfgpu_status dfgpu_ctx_synchronize(dfgpu_ctx *ctx);
 /* raw CUDA stream (cudaStream_t) every operator of this ctx launches on — for CUDA-event timing */
 void *dfgpu_ctx_stream(dfgpu_ctx *ctx);
+/* Per-kernel device timing (CUDA events recorded on the launching stream around every hot kernel;
+ * the analogue of the reference's per-operator metrics::Time).  profile_json writes
+ * [{"name","launches","ms","algo_bytes"},...] into buf and resets the records. */
+dfgpu_status dfgpu_ctx_set_profiling(dfgpu_ctx *ctx, int32_t enable);
+dfgpu_status dfgpu_ctx_profile_json(dfgpu_ctx *ctx, char *buf, int64_t cap);
 /* number of kernels this library launched on ctx so far (bench.py "gpu_launches") */
 int64_t dfgpu_ctx_kernel_launches(const dfgpu_ctx *ctx);
 /* pinned host memory for callers that want PCIe-speed uploads (bench e2e leg) */
