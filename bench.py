@@ -93,10 +93,39 @@ class Clocks:
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
-    def __init__(self, dev):
-        self.dev, self.p = dev, None
+    def __init__(self, dev, mode="nvml"):
+        self.dev, self.p, self.h, self.samples, self.mode = dev, None, None, [], mode
+        if mode == "nvml":
+            try:
+                import pynvml
+                pynvml.nvmlInit()
+                self.nv = pynvml
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                idx = int(vis.split(",")[dev]) if vis and vis.split(",")[dev].isdigit() else dev
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+                self.mx = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            except Exception:
+                self.h = None
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM),
+                                     nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)))
+            except Exception:
+                pass
+            self._stop.wait(0.02)
 
     def __enter__(self):
+        if self.mode == "off":
+            return self
+        if self.h is not None:
+            import threading
+            self._stop = threading.Event()
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
+            return self
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                                        "-i", str(self.dev)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -106,6 +135,21 @@ class Clocks:
 
     def __exit__(self, *a):
         self.result = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.mode != "off" and self.h is not None:
+            self._stop.set()
+            self._t.join()
+            nv = self.nv
+            if not self.samples:
+                self._loop_once = self.samples.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM),
+                                                       nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)))
+            bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksEventReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": nv.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksEventReasonSwPowerCap}
+            allr = 0
+            for _, r in self.samples:
+                allr |= r
+            self.result = {"sm_mhz": statistics.median([c for c, _ in self.samples]), "sm_max_mhz": self.mx,
+                           "reasons": sorted(k for k, b in bits.items() if allr & b), "samples": len(self.samples), "source": "nvml"}
+            return
         if not self.p:
             return
         time.sleep(0.15)
@@ -233,7 +277,7 @@ def run_ours(args):
             op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
             op.push(w["dev"])
             out = op.emit_device()
-            hold.append((op, out))
+            hold[:] = [(op, out)]
             return out
         # Partial -> hash repartition (NCCL all-to-all over NVLink) -> FinalPartitioned
         part = df.GpuAggregateExec(ctx, df.AggregateMode.Partial, w["schema"], w["group_by"], w["exprs"])
@@ -246,7 +290,7 @@ def run_ours(args):
         if recv is not None:
             fin.push(recv)
         out = fin.emit_device()
-        hold.append((part, st, recv, fin, out))
+        hold[:] = [(part, st, recv, fin, out)]
         return out
 
     for _ in range(args.warmup):
@@ -257,11 +301,15 @@ def run_ours(args):
     ctx.set_profiling(True)
     launches0 = ctx.kernel_launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with Clocks(local) as clk:
+    clk = Clocks(local, args.clocks)
+    host_ms = []
+    with clk:
         barrier()
         e0.record(stream)
         for _ in range(args.steps):
+            t0 = time.perf_counter()
             out = step_device()
+            host_ms.append(round((time.perf_counter() - t0) * 1e3, 2))
         e1.record(stream)
         barrier()
     ms = e0.elapsed_time(e1)
@@ -339,7 +387,7 @@ def run_ours(args):
                        f"Partial -> NCCL all-to-all -> FinalPartitioned (dp{world})"},
             "algorithmic_GBps": algo_bytes * world / (ms_per_step * 1e-3) / 1e9,
             "algorithmic_frac_of_peak": algo_bytes / (ms_per_step * 1e-3) / 1e9 / peak,
-            "clocks": clk.result, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+            "host_submit_ms": host_ms, "clocks": clk.result, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
         }
         print(json.dumps(line))
     if world > 1:
@@ -405,6 +453,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=["c2", "q1"])
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=50_000_000)
+    ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
