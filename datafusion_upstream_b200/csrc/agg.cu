@@ -15,6 +15,7 @@
 #include <chrono>
 
 #include "device.cuh"
+#include "fastagg.h"
 #include "groups.h"
 #include "ops.h"
 

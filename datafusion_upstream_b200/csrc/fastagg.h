@@ -1,0 +1,93 @@
+// fastagg.h — two-level, cardinality-oblivious grouped aggregation for keys whose packed image fits
+// 64 bits (GroupValuesPrimitive and short GroupValuesRows keys: group_values/primitive.rs:112-150,
+// row.rs:94-146) with accumulators that decompose into the state words of ops.h.
+//
+// It is the reference's own Partial -> hash repartition -> Final plan
+// (core/src/physical_planner.rs:814-849) applied INSIDE one GPU, at SM scale:
+//   level 1  every CTA pre-aggregates its rows in a shared-memory hash table (or, for <= 4 groups,
+//            in registers); rows whose key finds no room are spilled as single-row partial
+//            states.  At the end the table is flushed as partial-state records.  A histogram over
+//            the top hash bits of every record is kept on the side.
+//   scatter  records are radix-partitioned by those hash bits (count -> scan -> scatter).
+//   level 2  one CTA per partition merges its records in a shared-memory hash table and appends
+//            the finished groups (key image, state words, seen flags) to dense output arrays.
+// No table in HBM, no growth / rehash, no host round trip per batch, no global-atomic contention on
+// hot keys; HBM sees only streaming reads and writes.  Partitions that hold more distinct keys
+// than a level-2 table are handled by re-partitioning their overflow on the next hash bits.
+#pragma once
+#include "groups.h"
+#include "ops.h"
+
+namespace dfgpu {
+
+static const int FA_MAX_OPS = 24;
+static const int FA_MAX_KEYCOLS = 8;
+static const int FA_PBITS = 12;
+static const int FA_P = 1 << FA_PBITS;     // partitions per level
+static const uint64_t FA_EMPTY = ~0ULL;    // free-slot marker; the real key ~0 lives in side group 1
+
+struct FaKeyCol {
+    ColView v;
+    int32_t kind, off, w, null_bit;  // kind 0: fixed width, 1: bool
+};
+struct FaOp {
+    ColView val, filt;
+    int32_t kind, nwords, woff, seen_bit, has_val, has_filt, pad0, pad1;
+    uint64_t init_lo, init_hi;  // identity in the state representation of the HBM state arrays
+};
+// One launch's description: how to build the key image of a row and how to lift a row into each
+// accumulator.  Lives in device memory; every CTA copies it to shared memory.
+struct FaPlan {
+    FaKeyCol keys[FA_MAX_KEYCOLS];
+    FaOp ops[FA_MAX_OPS];
+    int32_t nkeys, direct, null_off, nops;
+    int32_t SW, RW, seen_word, pad;  // state words / record words (1 + SW) / index of the seen word or -1
+};
+
+struct FaOpSpec {
+    int kind = 0, nwords = 1;
+    int seen_bit = -1;  // ops sharing a NullState share the bit
+    uint64_t init_lo = 0, init_hi = 0;
+};
+
+struct FaResult {
+    int64_t G = 0;
+    BufRef keys;                // [G] key images
+    std::vector<BufRef> state;  // per op: [G * nwords]
+    std::vector<BufRef> seen;   // per seen bit: [G] bytes
+    int64_t null_gid = -1;      // group id of the NULL key of a single-column 8-byte key
+    int64_t empty_gid = -1;     // group id of the key whose image is ~0 (kept outside the hash tables)
+};
+
+class FastAgg {
+  public:
+    FastAgg(Ctx *ctx, const std::vector<FaOpSpec> &ops);
+    static bool kind_supported(int kind) { return kind != OP_MIN_I128 && kind != OP_MAX_I128; }
+    int SW() const { return SW_; }
+    int seen_word() const { return seen_word_; }
+    const std::vector<FaOpSpec> &ops() const { return ops_; }
+    int nbits() const { return nbits_; }
+
+    // Aggregate rows [0, n) described by `plan` (keys/ops column views already positioned at the
+    // first row; kind/nwords/woff/seen_bit/init fields are filled in here).
+    void push(FaPlan &plan, int64_t n, int64_t algo_bytes);
+    // Merge everything pushed so far into dense groups and leave the store empty.
+    FaResult finalize();
+    // finalize() + re-insert the groups as partial-state records; returns the exact group count.
+    int64_t compact();
+    size_t device_bytes() const;
+
+  private:
+    void ensure_capacity(int64_t more);
+    void reinsert(const FaResult &r);
+    Ctx *ctx_;
+    std::vector<FaOpSpec> ops_;
+    int SW_ = 0, RW_ = 0, seen_word_ = -1, nbits_ = 0;
+    int S1_ = 0, S2max_ = 0;
+    size_t smem1_ = 0, smem2_ = 0;
+    BufRef recs_, scalars_, hist_, side_, plan_dev_, mode_flag_;
+    int64_t cap_ = 0, used_ub_ = 0;
+    bool probed_ = false;
+};
+
+}  // namespace dfgpu

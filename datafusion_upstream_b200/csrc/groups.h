@@ -80,6 +80,23 @@ class GroupTable {
     KeyMode mode() const { return mode_; }
     void check_overflow();
 
+    // --- hooks for the two-level aggregation path (fastagg.h) ---------------------------------
+    struct KeyLayout { int kind, off, w, null_bit; bool dict; };
+    std::vector<KeyLayout> key_layout() const {
+        std::vector<KeyLayout> v;
+        for (auto &c : cols_) v.push_back(KeyLayout{c.kind, c.off, c.w, c.null_bit, c.type.id == T_DICT});
+        return v;
+    }
+    int null_off() const { return null_off_; }
+    // Take ownership of a dense key store produced elsewhere (U64 layouts only): emit_keys(G) then
+    // reads these images.  null_gid = id of the NULL-key group of a DIRECT table, or -1.
+    void adopt_dense(const BufRef &keys, int64_t null_gid) {
+        gkeys_ = keys;
+        tv_.gkeys = keys ? keys->as<uint64_t>() : nullptr;
+        adopted_ = true;
+        adopted_null_gid_ = null_gid;
+    }
+
   private:
     struct KeyCol {
         TypeInfo type;      // declared type (may be dictionary)
@@ -101,6 +118,8 @@ class GroupTable {
     BufRef slots_, gkeys_, grows_, heap_, goff_, glen_, scalars_;  // scalars: ngroups, overflow, heap_used
     int64_t groups_ub_ = 0;
     int64_t heap_cap_ = 0, heap_ub_ = 0;
+    bool adopted_ = false;
+    int64_t adopted_null_gid_ = -1;
 };
 
 }  // namespace dfgpu
