@@ -235,10 +235,50 @@ void PinnedPool::trim() {
 void *pinned_alloc(size_t n) { return pinned_pool().alloc(n); }
 void pinned_free(void *p) { pinned_pool().release(p); }
 
+size_t BufCache::size_class(size_t n) {
+    if (n < ((size_t)256 << 10)) return 0;
+    size_t p = (size_t)1 << (63 - __builtin_clzll((unsigned long long)n));
+    size_t step = p >> 3;  // 8 classes per octave: <= 12.5% internal waste
+    return (n + step - 1) / step * step;
+}
+void *BufCache::take(size_t cls) {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = free_list.find(cls);
+    if (it == free_list.end()) return nullptr;
+    void *p = it->second;
+    free_list.erase(it);
+    cached -= cls;
+    return p;
+}
+bool BufCache::give(size_t cls, void *p) {
+    std::lock_guard<std::mutex> g(mu);
+    if (cached + cls > limit) return false;
+    free_list.emplace(cls, p);
+    cached += cls;
+    return true;
+}
+void BufCache::trim(cudaStream_t st) {
+    std::lock_guard<std::mutex> g(mu);
+    for (auto &kv : free_list) cudaFreeAsync(kv.second, st);
+    free_list.clear();
+    cached = 0;
+}
+
 DevBuf::DevBuf(Ctx *c, size_t n, bool zero) : ctx(c), bytes(n) {
     if (n == 0) return;
-    cudaError_t e = cudaMallocAsync(&ptr, n, c->stream);
+    cls = BufCache::size_class(n);
+    if (cls) ptr = c->bufs.take(cls);
+    cudaError_t e = cudaSuccess;
+    if (!ptr) {
+        e = cudaMallocAsync(&ptr, cls ? cls : n, c->stream);
+        if (e != cudaSuccess) {  // give the cached blocks back to the pool and retry once
+            cudaGetLastError();
+            c->bufs.trim(c->stream);
+            e = cudaMallocAsync(&ptr, cls ? cls : n, c->stream);
+        }
+    }
     if (e != cudaSuccess) {
+        ptr = nullptr;
         cudaGetLastError();
         // ResourcesExhausted, like MemoryReservation::try_grow failing (hash_join.rs:708,738)
         fail(DFGPU_RESOURCES_EXHAUSTED, "Resources exhausted: failed to allocate " + std::to_string(n) +
@@ -247,7 +287,9 @@ DevBuf::DevBuf(Ctx *c, size_t n, bool zero) : ctx(c), bytes(n) {
     if (zero) DF_CUDA(cudaMemsetAsync(ptr, 0, n, c->stream));
 }
 DevBuf::~DevBuf() {
-    if (ptr) cudaFreeAsync(ptr, ctx->stream);
+    if (!ptr || parent) return;
+    if (cls && ctx->bufs.give(cls, ptr)) return;
+    cudaFreeAsync(ptr, ctx->stream);
 }
 
 ColView DevCol::view() const {

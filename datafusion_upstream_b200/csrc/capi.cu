@@ -51,6 +51,8 @@ void ctx_release(Ctx *c) {
     if (c->refs.fetch_sub(1) != 1) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    c->bufs.trim(c->stream);
+    cudaStreamSynchronize(c->stream);
     ctx_destroy_nccl(c);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -132,6 +134,10 @@ dfgpu_status dfgpu_ctx_create(const dfgpu_options *opts, dfgpu_ctx **out) {
     DF_CUDA(cudaDeviceGetDefaultMemPool(&pool, o.device));
     uint64_t thresh = UINT64_MAX;
     DF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+    {
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) c->bufs.limit = total_b / 3;
+    }
     if (o.world > 1) ctx_init_nccl(c.get());
     *out = c.release();
     DF_CATCH

@@ -93,6 +93,21 @@ struct PinnedPool {
     void trim();
 };
 
+// Size-class cache of device blocks in front of the stream-ordered allocator.  An operator step
+// allocates the same multi-GB scratch buffers (record store, partition buffer, outputs) every
+// time; cudaMallocAsync takes milliseconds when its pool has to carve or map such a block, so
+// freed blocks >= 256 KiB are kept here and handed back without a driver call.  Safe because all
+// work of a context is ordered on its one stream.
+struct BufCache {
+    std::mutex mu;
+    std::multimap<size_t, void *> free_list;
+    size_t cached = 0, limit = (size_t)48 << 30;
+    static size_t size_class(size_t n);  // 0: not cached
+    void *take(size_t cls);
+    bool give(size_t cls, void *p);      // false: cache full, caller frees
+    void trim(cudaStream_t st);
+};
+
 }  // namespace dfgpu
 
 struct dfgpu_ctx {
@@ -106,6 +121,7 @@ struct dfgpu_ctx {
     int64_t h2d_bytes = 0, d2h_bytes = 0, nvlink_bytes = 0;
     void *nccl_comm = nullptr;  // ncclComm_t
     dfgpu::PinnedPool pinned;
+    dfgpu::BufCache bufs;
     uint64_t *flush_dummy = nullptr;
     std::atomic<int> refs{1};  // the creator's handle + every batch / operator created on this ctx
     // optional per-kernel CUDA-event timing (bench.py roofline): name -> (events, launches)
@@ -164,7 +180,9 @@ struct DevBuf {
     Ctx *ctx = nullptr;
     void *ptr = nullptr;
     size_t bytes = 0;
+    size_t cls = 0;  // size class when the block came from / returns to the context's BufCache
     DevBuf() {}
+    std::shared_ptr<DevBuf> parent;  // set for views: the memory belongs to (and lives as long as) parent
     DevBuf(Ctx *c, size_t n, bool zero = false);
     ~DevBuf();
     DevBuf(const DevBuf &) = delete;
@@ -173,6 +191,15 @@ struct DevBuf {
 };
 typedef std::shared_ptr<DevBuf> BufRef;
 inline BufRef make_buf(Ctx *c, size_t n, bool zero = false) { return std::make_shared<DevBuf>(c, n, zero); }
+// non-owning window [off, off + n) of another buffer
+inline BufRef make_view(const BufRef &parent, size_t off, size_t n) {
+    BufRef v = std::make_shared<DevBuf>();
+    v->ctx = parent->ctx;
+    v->ptr = (uint8_t *)parent->ptr + off;
+    v->bytes = n;
+    v->parent = parent;
+    return v;
+}
 
 // POD view handed to kernels
 struct ColView {

@@ -8,6 +8,9 @@
 // Integer state arithmetic is associative, so the order in which partial states are merged cannot
 // change a result bit; Float64 sums differ from the row-order sum only within the 1e-9 contract.
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 #include "device.cuh"
 #include "fastagg.h"

@@ -71,6 +71,8 @@ class FastAgg {
     // Aggregate rows [0, n) described by `plan` (keys/ops column views already positioned at the
     // first row; kind/nwords/woff/seen_bit/init fields are filled in here).
     void push(FaPlan &plan, int64_t n, int64_t algo_bytes);
+    // Size the record store once for a batch of `rows` rows pushed in `launches` chunks.
+    void reserve(int64_t rows, int64_t launches);
     // Merge everything pushed so far into dense groups and leave the store empty.
     FaResult finalize();
     // finalize() + re-insert the groups as partial-state records; returns the exact group count.
