@@ -20,6 +20,7 @@ namespace dfgpu {
 static const int FA_T1 = 512;   // level-1 threads per CTA (2 CTAs / SM)
 static const int FA_R1 = 4;     // rows per thread per tile
 static const int FA_T2 = 1024;  // level-2 threads per CTA (1 CTA / SM)
+static const int FA_CSTRIDE = 32; // scatter cursors live 128 B apart: same-line atomics serialise in L2
 
 struct FaStore {
     uint64_t *recs;
@@ -60,8 +61,12 @@ DF_D void fa_load_key(const FaPlan &pl, int64_t row, uint64_t &key, int &side) {
                 key |= 1ULL << (8 * pl.null_off + kc.null_bit);
                 continue;
             }
-            uint64_t v = col_bits64(kc.v, row);
-            if (kc.w < 8) v &= (1ULL << (8 * kc.w)) - 1;
+            uint64_t v;  // raw little-endian bytes of the value, zero-extended
+            if (kc.kind == 1) v = bit_get((const uint8_t *)kc.v.values, kc.v.dbit + row) ? 1 : 0;
+            else if (kc.w == 1) v = ((const uint8_t *)kc.v.values)[row];
+            else if (kc.w == 2) v = ((const uint16_t *)kc.v.values)[row];
+            else if (kc.w == 4) v = ((const uint32_t *)kc.v.values)[row];
+            else v = ((const uint64_t *)kc.v.values)[row];
             key |= v << (8 * kc.off);
         }
     }
@@ -86,26 +91,27 @@ DF_D double fa_as_f64(const ColView &c, int64_t i) {
 }
 // Lift an accepted row into the state representation.  Returns false when the value must not be
 // combined (NaN under MIN/MAX: the strict compare is never true) — the seen bit is still set.
-DF_D bool fa_lift(const FaOp &op, int64_t row, uint64_t &lo, uint64_t &hi) {
+DF_D bool fa_lift_kv(int kind, const ColView &val, int64_t row, uint64_t &lo, uint64_t &hi) {
     hi = 0;
-    switch (op.kind) {
+    switch (kind) {
     case OP_COUNT: lo = 1; return true;
-    case OP_ADD_F64: lo = (uint64_t)__double_as_longlong(fa_as_f64(op.val, row)); return true;
+    case OP_ADD_F64: lo = (uint64_t)__double_as_longlong(fa_as_f64(val, row)); return true;
     case OP_ADD_I128: {
-        uint4 v = ld_stream_u128((const uint8_t *)op.val.values + 16 * row);
+        uint4 v = ld_stream_u128((const uint8_t *)val.values + 16 * row);
         lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
         hi = (uint64_t)v.z | ((uint64_t)v.w << 32);
         return true;
     }
     case OP_MIN_F64: case OP_MAX_F64: {
-        double d = fa_as_f64(op.val, row);
+        double d = fa_as_f64(val, row);
         if (!(d == d)) return false;
         lo = f64_to_ordered(d);
         return true;
     }
-    default: lo = col_bits64(op.val, row); return true;  // ADD_COUNT, ADD_I64, MIN/MAX I64/U64
+    default: lo = col_bits64(val, row); return true;  // ADD_COUNT, ADD_I64, MIN/MAX I64/U64
     }
 }
+DF_D bool fa_lift(const FaOp &op, int64_t row, uint64_t &lo, uint64_t &hi) { return fa_lift_kv(op.kind, op.val, row, lo, hi); }
 
 // ---- combining into shared memory (native 32-bit atomics with exact carry forwarding) ----------
 DF_D void sm_add_limbs(uint32_t *p0, uint32_t *p1, uint32_t *p2, uint32_t *p3, uint64_t lo, uint64_t hi, int nlimbs) {
@@ -371,5 +377,6 @@ __global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ p
 
 }  // namespace dfgpu
 
+#include "fastagg_reg.inc"
 #include "fastagg_l2.inc"
 #include "fastagg_host.inc"

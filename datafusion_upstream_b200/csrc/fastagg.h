@@ -44,6 +44,20 @@ struct FaPlan {
     int32_t SW, RW, seen_word, pad;  // state words / record words (1 + SW) / index of the seen word or -1
 };
 
+// register mode of level 1 (fastagg_reg.inc)
+static const int FA_G0 = 4;         // groups held in registers
+static const int FA_MAXROLES = 12;  // accumulators that need a value load: one warp role each
+static const int FA_MAXLIGHT = 4;   // accept-only accumulators (COUNT) riding on role 0
+static const int FA_RR = 8;         // rows per thread per tile
+struct FaRegPlan {
+    int32_t nheavy, nlight, nroles, slabs;
+    int32_t heavy[FA_MAXROLES];        // logical op that defines heavy accumulator i
+    int32_t light[FA_MAXLIGHT];
+    uint32_t heavy_seen[FA_MAXROLES];  // seen bits of every logical op computed by accumulator i
+    int32_t heavy_woff[FA_MAXROLES], light_woff[FA_MAXLIGHT];  // word offsets in the CTA's partial record
+    int32_t alias[FA_MAX_OPS];         // logical op -> word offset of the accumulator that computes it
+};
+
 struct FaOpSpec {
     int kind = 0, nwords = 1;
     int seen_bit = -1;  // ops sharing a NullState share the bit
@@ -87,9 +101,9 @@ class FastAgg {
     int SW_ = 0, RW_ = 0, seen_word_ = -1, nbits_ = 0;
     int S1_ = 0, S2max_ = 0;
     size_t smem1_ = 0, smem2_ = 0;
-    BufRef recs_, scalars_, hist_, side_, plan_dev_, mode_flag_;
+    BufRef recs_, scalars_, hist_, side_, plan_dev_, regplan_dev_, mode_flag_;
     int64_t cap_ = 0, used_ub_ = 0;
-    bool probed_ = false;
+    bool reg_mode_allowed_ = true;
 };
 
 }  // namespace dfgpu
