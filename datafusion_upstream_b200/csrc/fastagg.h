@@ -46,16 +46,14 @@ struct FaPlan {
 
 // register mode of level 1 (fastagg_reg.inc)
 static const int FA_G0 = 4;         // groups held in registers
-static const int FA_MAXROLES = 12;  // accumulators that need a value load: one warp role each
-static const int FA_MAXLIGHT = 4;   // accept-only accumulators (COUNT) riding on role 0
+static const int FA_MAXROLES = 16;  // distinct accumulators of a launch: one warp role each
 static const int FA_RR = 8;         // rows per thread per tile
 struct FaRegPlan {
-    int32_t nheavy, nlight, nroles, slabs;
-    int32_t heavy[FA_MAXROLES];        // logical op that defines heavy accumulator i
-    int32_t light[FA_MAXLIGHT];
-    uint32_t heavy_seen[FA_MAXROLES];  // seen bits of every logical op computed by accumulator i
-    int32_t heavy_woff[FA_MAXROLES], light_woff[FA_MAXLIGHT];  // word offsets in the CTA's partial record
-    int32_t alias[FA_MAX_OPS];         // logical op -> word offset of the accumulator that computes it
+    int32_t nacc, slabs;
+    int32_t op[FA_MAXROLES];      // logical op that defines accumulator i
+    uint32_t seen[FA_MAXROLES];   // seen bits of every logical op computed by accumulator i
+    int32_t woff[FA_MAXROLES];    // word offset in the CTA's partial record
+    int32_t alias[FA_MAX_OPS];    // logical op -> word offset of the accumulator that computes it
 };
 
 struct FaOpSpec {
