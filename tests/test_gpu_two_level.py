@@ -1,0 +1,165 @@
+"""Parity of the two-level aggregation path (fastagg.h: shared-memory / register pre-aggregation,
+radix partition, per-partition merge) with the oracle, on every key shape it accepts, in every
+level-1 mode, with overflow rounds and spills forced, and against the table path on the same input.
+
+The library picks the path itself (64-bit key images, no MIN/MAX over Decimal128, no memory limit);
+the environment hooks below only shrink its tables so the rare branches run on small inputs.
+"""
+import numpy as np
+import pyarrow as pa
+import pytest
+
+from gpu_helpers import gpu_agg, gpu_ctx, oracle_agg, random_keys
+from test_gpu_agg import SPECS, make_table
+from util import assert_rows_equal, assert_tables_equal, rows_of
+
+pytestmark = pytest.mark.gpu
+
+# everything the two-level path supports: MIN/MAX over Decimal128 (128-bit CAS state) stays on the table path
+FAST_SPECS = [s for s in SPECS if not (s[0] in ("min", "max") and s[1] in ("d", "big"))]
+FAST_KEYS = [["int64"], ["int64_small"], ["uint64"], ["int32"], ["int16", "int8"], ["float32"], ["date32"], ["timestamp"],
+             ["uint8", "uint8"], ["int32", "int16", "bool"], ["bool"], ["float64"]]
+
+HOOKS = {
+    "default": {},
+    "tiny_tables": {"DFGPU_FA_S2MAX": "64", "DFGPU_FA_S1": "32"},    # spills at level 1, overflow rounds at level 2
+    "no_register_mode": {"DFGPU_FA_NOREG": "1"},
+    "table_path": {"DFGPU_DISABLE_TWO_LEVEL": "1"},                   # same specs through GroupTable + k_accumulate
+}
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = gpu_ctx()
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("hook", list(HOOKS), ids=list(HOOKS))
+@pytest.mark.parametrize("card", [3, 37, 5000], ids=lambda c: f"card{c}")
+@pytest.mark.parametrize("keys", FAST_KEYS, ids=["+".join(k) for k in FAST_KEYS])
+def test_single_vs_oracle(ctx, monkeypatch, keys, card, hook):
+    for k, v in HOOKS[hook].items():
+        monkeypatch.setenv(k, v)
+    rng = np.random.default_rng(sum(map(ord, "".join(keys))) + card)
+    nulls = card != 37
+    batches = [make_table(rng, n, keys, card, 0.1 if nulls else 0.0, 0.15 if nulls else 0.0) for n in (3000, 1, 0, 9001)]
+    gk = [f"k{i}" for i in range(len(keys))]
+    got = gpu_agg(ctx, "single", batches, gk, FAST_SPECS)
+    want = oracle_agg("single", batches, gk, FAST_SPECS)
+    assert_tables_equal(got, want, key_cols=list(range(len(keys))), what=f"{keys} card={card} {hook}")
+
+
+@pytest.mark.parametrize("hook", ["default", "tiny_tables"])
+@pytest.mark.parametrize("keys", [["int64_small"], ["int16", "int8"], ["uint8", "uint8"]], ids=lambda k: "+".join(k))
+def test_partial_final_vs_oracle(ctx, monkeypatch, keys, hook):
+    for k, v in HOOKS[hook].items():
+        monkeypatch.setenv(k, v)
+    rng = np.random.default_rng(23)
+    gk = [f"k{i}" for i in range(len(keys))]
+    parts = [[make_table(rng, n, keys, 211, 0.05, 0.1) for n in (1500, 700)] for _ in range(3)]
+    g_states = [gpu_agg(ctx, "partial", p, gk, FAST_SPECS) for p in parts]
+    o_states = [oracle_agg("partial", p, gk, FAST_SPECS) for p in parts]
+    for gs, os_ in zip(g_states, o_states):
+        assert_tables_equal(gs, os_, key_cols=list(range(len(keys))), what="partial state")
+    fin = [(f, None, n, None) for f, _, n, _ in FAST_SPECS]
+    got = gpu_agg(ctx, "final_partitioned", g_states, list(range(len(keys))), fin)
+    want = oracle_agg("final_partitioned", o_states, list(range(len(keys))), fin)
+    assert_tables_equal(got, want, key_cols=list(range(len(keys))), what="final")
+    single = oracle_agg("single", [b for p in parts for b in p], gk, FAST_SPECS)
+    assert_rows_equal(rows_of(got), rows_of(single), key_cols=list(range(len(keys))))
+
+
+def test_side_groups_null_and_all_ones_key(ctx):
+    """The NULL key and the key whose image is 0xFFFF_FFFF_FFFF_FFFF (-1) live outside the hash tables."""
+    rng = np.random.default_rng(3)
+    n = 50_000
+    raw = rng.integers(-2, 3, n)                      # -2..2: includes -1
+    keys = pa.array(raw, pa.int64(), mask=rng.random(n) < 0.2)
+    v = pa.array(rng.integers(-1000, 1000, n), pa.int64(), mask=rng.random(n) < 0.1)
+    b = pa.record_batch([keys, v], names=["k", "v"])
+    specs = [("count", None, "c", None), ("count", "v", "cv", None), ("sum", "v", "s", None), ("min", "v", "mn", None),
+             ("max", "v", "mx", None), ("avg", "v", "a", None)]
+    for mode_batches in ([b], [b.slice(0, 7), b.slice(7, 20_000), b.slice(20_007)]):
+        got = gpu_agg(ctx, "single", mode_batches, ["k"], specs)
+        want = oracle_agg("single", [b], ["k"], specs)
+        assert got.num_rows == 6
+        assert_tables_equal(got, want, key_cols=[0])
+    # only side groups present
+    only = pa.record_batch([pa.array([-1, None, -1, None], pa.int64()), pa.array([1, 2, 3, 4], pa.int64())], names=["k", "v"])
+    assert_tables_equal(gpu_agg(ctx, "single", [only], ["k"], specs), oracle_agg("single", [only], ["k"], specs), key_cols=[0])
+
+
+def test_register_mode_q1_shape_and_late_keys(ctx):
+    """Q1 shape with fixed-width keys (register mode), value nulls, a filter, and keys that first
+    appear after the sample the device used to choose the mode (exact per-row slow path)."""
+    import decimal
+    rng = np.random.default_rng(9)
+    n = 120_000
+    pick = rng.choice(4, n, p=[0.25, 0.006, 0.493, 0.251])
+    flag = np.array([65, 78, 78, 82], np.uint8)[pick]
+    status = np.array([70, 70, 79, 70], np.uint8)[pick]
+    flag[100_000:100_050] = 90          # a 5th and 6th group long after the probe sample
+    status[110_000:110_010] = 91
+    dec = lambda lo, hi, p, s, nf: pa.array([decimal.Decimal(int(x)).scaleb(-s) for x in rng.integers(lo, hi, n)], pa.decimal128(p, s),
+                                            mask=(rng.random(n) < nf) if nf else None)
+    b = pa.record_batch([pa.array(flag), pa.array(status, pa.uint8(), mask=np.arange(n) == 115_000), dec(100, 5001, 15, 2, 0),
+                         dec(90000, 10495001, 15, 2, 0.05),
+                         pa.array([decimal.Decimal(int(a) * 10**13 + int(c)).scaleb(-6) for a, c in
+                                   zip(rng.integers(-(10**17), 10**17, n), rng.integers(0, 10**13, n))], pa.decimal128(38, 6)),
+                         pa.array(rng.random(n) < 0.5),
+                         pa.array(rng.normal(size=n))],
+                        names=["f", "s", "qty", "price", "charge", "flt", "x"])
+    specs = [("sum", "qty", "sum_qty", None), ("avg", "qty", "avg_qty", None), ("sum", "price", "sum_price", None),
+             ("avg", "price", "avg_price", None), ("sum", "charge", "sum_charge", None), ("count", None, "cnt", None),
+             ("count", "price", "cnt_price", None), ("sum", "qty", "sum_qty_f", "flt"), ("min", "x", "min_x", None),
+             ("avg", "x", "avg_x", None)]
+    got = gpu_agg(ctx, "single", [b], ["f", "s"], specs)
+    want = oracle_agg("single", [b], ["f", "s"], specs)
+    assert got.num_rows == want.num_rows and got.num_rows > 4
+    assert_tables_equal(got, want, key_cols=[0, 1])
+
+
+def test_num_groups_mid_stream_then_more_input(ctx):
+    """num_groups() compacts the record store; the operator keeps accepting input afterwards."""
+    import datafusion_upstream_b200 as df
+    rng = np.random.default_rng(4)
+    mk = lambda n: pa.record_batch([random_keys(rng, n, "int64_small", 1000, 0.05), pa.array(rng.integers(0, 9, n), pa.int64())], names=["k", "v"])
+    b1, b2 = mk(20_000), mk(30_000)
+    op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, b1.schema, ["k"],
+                             [df.AggregateExpr(df.AggFunc.Count, None, "c"), df.AggregateExpr(df.AggFunc.Sum, "v", "s"),
+                              df.AggregateExpr(df.AggFunc.Avg, "v", "a")])
+    op.push(b1)
+    g1 = op.num_groups()
+    assert g1 == len(set(b1.column(0).to_pylist()))
+    op.push(b2)
+    assert op.num_groups() == len(set(b1.column(0).to_pylist()) | set(b2.column(0).to_pylist()))
+    got = op.emit()
+    op.close()
+    want = oracle_agg("single", [b1, b2], ["k"], [("count", None, "c", None), ("sum", "v", "s", None), ("avg", "v", "a", None)])
+    assert_tables_equal(got, want, key_cols=[0])
+
+
+@pytest.mark.parametrize("dist", ["zipf", "uniform", "all_distinct"])
+def test_clickbench_shape_properties_at_scale(ctx, dist):
+    """Config C2 at 20 M rows (too big for the oracle in seconds): size-independent properties —
+    counts add up to the row count, keys are distinct, group count equals numpy's, and a checksum of
+    (key * count) matches the checksum of the input keys."""
+    rng = np.random.default_rng(8)
+    n = 20_000_000
+    if dist == "zipf":
+        r = np.exp(rng.random(n) * np.log(8_000_000)).astype(np.uint64)
+    elif dist == "uniform":
+        r = rng.integers(0, 3_000_000, n).astype(np.uint64)
+    else:
+        r = np.arange(n, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        keys = (r * np.uint64(0x9E3779B97F4A7C15)).view(np.int64)
+    b = pa.record_batch([pa.array(keys)], names=["UserID"])
+    got = gpu_agg(ctx, "single", [b], ["UserID"], [("count", None, "COUNT(*)", None)])
+    k = got.column(0).to_numpy()
+    c = got.column(1).to_numpy()
+    assert c.sum() == n
+    assert len(np.unique(k)) == len(k) == len(np.unique(keys))
+    with np.errstate(over="ignore"):
+        assert (k.view(np.uint64) * c.astype(np.uint64)).sum() == keys.view(np.uint64).sum()
