@@ -55,7 +55,7 @@ def _mix64_torch(x):
     return x
 
 
-def gen_c2_keys(n, seed, device, universe=40_000_000):
+def gen_c2_keys(n, seed, device, universe=85_000_000):
     """Zipf(s~1) ranks (log-uniform inverse CDF) over `universe` ids, mapped through a 64-bit bijective
     mixer so keys are sparse 64-bit values like real UserIDs."""
     import torch
@@ -185,7 +185,7 @@ def build_workload(args, df, ctx, torch, device, rank):
     if args.workload == "c2":
         keys = gen_c2_keys(n, 42 + rank, device)
         schema = pa.schema([("UserID", pa.int64())])
-        w["name"] = f"ClickBench-shaped GROUP BY UserID COUNT(*), {n} Int64 rows, Zipf(1.0) over 40M ids (BASELINE configs[1])"
+        w["name"] = f"ClickBench-shaped GROUP BY UserID COUNT(*), {n} Int64 rows, Zipf(1.0) over 85M ids (BASELINE configs[1])"
         w["dev"] = df.DeviceBatch.from_device(ctx, schema, [{"buffers": [None, keys.data_ptr()], "null_count": 0}], n, keep=keys)
         w["schema"] = schema
         w["group_by"] = ["UserID"]
@@ -271,17 +271,18 @@ def run_ours(args):
 
     hold = []
 
-    def step_device():
-        """One pass of the hot path, inputs resident in HBM, result left in HBM."""
+    def step(inp, to_host=False):
+        """One pass of the hot path over one batch.  inp: DeviceBatch (inputs resident in HBM) or a pinned
+        host RecordBatch (H2D inside the step); to_host: read the result back into host Arrow buffers."""
         if world == 1:
             op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
-            op.push(w["dev"])
-            out = op.emit_device()
+            op.push(inp)
+            out = op.emit() if to_host else op.emit_device()
             hold[:] = [(op, out)]
             return out
         # Partial -> hash repartition (NCCL all-to-all over NVLink) -> FinalPartitioned
         part = df.GpuAggregateExec(ctx, df.AggregateMode.Partial, w["schema"], w["group_by"], w["exprs"])
-        part.push(w["dev"])
+        part.push(inp)
         st = part.emit_device()
         rp = df.GpuRepartitionExec(ctx, part.schema, list(range(len(w["group_by"]))), world)
         recv = rp.exchange(rp.partition_device(st))
@@ -289,9 +290,12 @@ def run_ours(args):
                                   [df.AggregateExpr(e.func, None, e.name) for e in w["exprs"]])
         if recv is not None:
             fin.push(recv)
-        out = fin.emit_device()
+        out = fin.emit() if to_host else fin.emit_device()
         hold[:] = [(part, st, recv, fin, out)]
         return out
+
+    def step_device():
+        return step(w["dev"])
 
     for _ in range(args.warmup):
         out = step_device()
@@ -330,24 +334,29 @@ def run_ours(args):
 
     # ---- e2e: host (pinned) Arrow buffers through the C-ABI, H2D + D2H inside the timed region ----
     e2e = None
-    if world == 1 and not args.no_e2e:
+    if not args.no_e2e:
         hb, keep, h2d = pinned_batch(ctx, w["schema"], w["host_cols"], n, torch)
         e2e_steps = max(1, min(args.steps, 5))
-
-        def step_host():
-            op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
-            op.push(hb)
-            res = op.emit()         # D2H into pinned buffers + Arrow import
-            op.close()
-            return res
-        step_host()
+        step(hb, to_host=True)
+        hold.clear()
         barrier()
         t0 = time.perf_counter()
+        res = None
         for _ in range(e2e_steps):
-            res = step_host()
+            res = None
+            hold.clear()            # the consumer drops the previous result: its pinned buffers return to the pool
+            res = step(hb, to_host=True)
         barrier()
         dt = (time.perf_counter() - t0) / e2e_steps
-        e2e = {"value": n / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(res.nbytes), "ms_per_step": dt * 1e3}
+        d2h = int(res.nbytes)
+        hold.clear()
+        if world > 1:
+            t = torch.tensor([dt, float(h2d), float(d2h)], dtype=torch.float64)
+            tmax = t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t)
+            dt, h2d, d2h = float(tmax[0]), int(t[1]), int(t[2])
+        e2e = {"value": n * world / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3}
         del hb
         for p in keep:
             ctx.host_free(p)
@@ -408,7 +417,7 @@ def run_reference(args):
     rng = np.random.default_rng(42)
     if args.workload == "c2":
         u = rng.random(n)
-        rank_ = np.exp(u * math.log(40_000_000)).astype(np.int64)
+        rank_ = np.exp(u * math.log(85_000_000)).astype(np.int64)
         with np.errstate(over="ignore"):
             x = rank_.astype(np.uint64)
             x ^= x >> np.uint64(30); x *= np.uint64(0xbf58476d1ce4e5b9)
@@ -416,7 +425,7 @@ def run_reference(args):
             x ^= x >> np.uint64(31)
         keys = x.view(np.int64)
         run = lambda: oracle.bench_groupby_count_i64(keys, threads)
-        name = f"ClickBench-shaped GROUP BY UserID COUNT(*), {args.rows} Int64 rows, Zipf(1.0) over 40M ids (BASELINE configs[1])"
+        name = f"ClickBench-shaped GROUP BY UserID COUNT(*), {args.rows} Int64 rows, Zipf(1.0) over 85M ids (BASELINE configs[1])"
     else:
         pick = rng.choice(4, n, p=[0.25, 0.006, 0.493, 0.251])
         flag = np.array([65, 78, 78, 82], np.uint8)[pick]

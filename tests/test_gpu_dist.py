@@ -1,0 +1,112 @@
+"""Two-GPU parity of the sharded path (needs >= 2 GPUs; skipped otherwise): Partial on each rank's row range
+-> `dfgpu_partition_hash` -> `dfgpu_exchange_all_to_all` (NCCL) -> FinalPartitioned, against the oracle's Single
+aggregation of the whole table.  Also the join exchange: both sides repartitioned by key owner, per-rank
+Partitioned joins, union equals the oracle's join."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _table(seed, n):
+    rng = np.random.default_rng(seed)
+    k1 = pa.array(rng.integers(-50, 5000, n), pa.int64(), mask=rng.random(n) < 0.02)
+    k2 = pa.array(rng.integers(0, 3, n).astype(np.int16), pa.int16())
+    v = pa.array(rng.integers(-10**6, 10**6, n), pa.int64(), mask=rng.random(n) < 0.1)
+    f = pa.array(rng.normal(size=n))
+    return pa.record_batch([k1, k2, v, f], names=["k1", "k2", "v", "f"])
+
+
+SPECS = [("count", None, "COUNT(*)", None), ("sum", "v", "SUM(v)", None), ("avg", "f", "AVG(f)", None), ("min", "v", "MIN(v)", None),
+         ("max", "f", "MAX(f)", None)]
+
+
+def _worker(rank, world, port, n_rows, out_q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import datafusion_upstream_b200 as df
+        from datafusion_upstream_b200.dist import bootstrap_nccl_id, shard_range, sharded_aggregate
+        uid = bootstrap_nccl_id(dist, df.GpuContext.nccl_unique_id)
+        ctx = df.GpuContext(device=rank, rank=rank, world=world, nccl_unique_id=uid)
+        full = _table(11, n_rows)
+        lo, hi = shard_range(n_rows, rank, world)
+        mine = full.slice(lo, hi - lo)
+        exprs = [df.AggregateExpr(df.AggFunc[f.capitalize()], a, nm) for f, a, nm, _ in SPECS]
+        out = sharded_aggregate(ctx, full.schema, ["k1", "k2"], exprs, [mine.slice(0, 1000), mine.slice(1000)], world)
+        # join: repartition both sides by key owner, join locally
+        left = pa.record_batch([pa.array(np.arange(3000, dtype=np.int64) % 1500), pa.array(np.arange(3000, dtype=np.int32))], names=["a", "x"])
+        right = pa.record_batch([pa.array((np.arange(9000, dtype=np.int64) * 7) % 2000), pa.array(np.arange(9000, dtype=np.int32))], names=["b", "y"])
+        llo, lhi = shard_range(left.num_rows, rank, world)
+        rlo, rhi = shard_range(right.num_rows, rank, world)
+        lp = df.GpuRepartitionExec(ctx, left.schema, ["a"], world)
+        rpx = df.GpuRepartitionExec(ctx, right.schema, ["b"], world)
+        lmine = lp.exchange(lp.partition_device(left.slice(llo, lhi - llo)))
+        rmine = rpx.exchange(rpx.partition_device(right.slice(rlo, rhi - rlo)))
+        j = df.GpuHashJoinExec(ctx, left.schema, right.schema, [("a", "b")], df.JoinType.Inner, df.PartitionMode.Partitioned)
+        jout = j.execute([lmine] if lmine is not None else [], [rmine] if rmine is not None else [])
+        jrows = sum(b.num_rows for b in jout)
+        jsum = int(sum(int(np.sum(b.column(1).to_numpy().astype(np.int64) * 31 + b.column(3).to_numpy())) for b in jout))
+        import io
+        sink = io.BytesIO()
+        with pa.ipc.new_stream(sink, out.schema) as w:
+            w.write_batch(out)
+        res = [None] * world
+        dist.all_gather_object(res, (sink.getvalue(), jrows, jsum))
+        if rank == 0:
+            out_q.put(res)
+        ctx.synchronize()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_two_gpu_sharded_aggregate_and_join():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    import oracle
+    from gpu_helpers import oracle_agg
+    from util import assert_rows_equal, rows_of
+    world, n_rows = 2, 200_003
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_worker, args=(r, world, port, n_rows, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=500)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    rows = []
+    for buf, _, _ in res:
+        for b in pa.ipc.open_stream(buf).read_all().to_batches():
+            rows += rows_of(b)
+    want = oracle_agg("single", [_table(11, n_rows)], ["k1", "k2"], SPECS)
+    assert_rows_equal(rows, rows_of(want), key_cols=[0, 1])
+    # join: row count and a checksum over (x, y) equal the oracle's
+    left = pa.table({"a": np.arange(3000, dtype=np.int64) % 1500, "x": np.arange(3000, dtype=np.int32)})
+    right = pa.table({"b": (np.arange(9000, dtype=np.int64) * 7) % 2000, "y": np.arange(9000, dtype=np.int32)})
+    oj = oracle.hash_join("inner", left.to_batches(), right.to_batches(), [("a", "b")])
+    assert sum(r[1] for r in res) == oj.num_rows
+    assert sum(r[2] for r in res) == int(np.sum(oj.column(1).to_numpy().astype(np.int64) * 31 + oj.column(3).to_numpy()))
