@@ -404,6 +404,165 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def gen_join(n_build, n_probe, seed, device, rank=0, world=1):
+    """Q3-shaped join #2 at SF10 (post-filter): build = (o_orderkey, o_orderdate, o_shippriority) of the orders that
+    survived join #1, probe = (l_orderkey, l_extendedprice, l_discount) of the filtered lineitem rows.  Order keys
+    are sparse like TPC-H's (8 of every 32); ~10 % of the probe rows find a build row."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    n_orders = 15_000_000
+    allk = torch.arange(0, n_orders, device=device, dtype=torch.int64)
+    allk = (allk // 8) * 32 + (allk % 8) + 1
+    perm = torch.randperm(n_orders, generator=g, device=device)
+    bkeys = allk[perm[:n_build]].contiguous()
+    odate = torch.randint(8035, 9204, (n_build,), generator=g, device=device, dtype=torch.int32)
+    oprio = torch.zeros(n_build, device=device, dtype=torch.int32)
+    gp = torch.Generator(device=device)
+    gp.manual_seed(seed + 1000 + rank)
+    pk = allk[torch.randint(0, n_orders, (n_probe,), generator=gp, device=device)].contiguous()
+
+    def dec(lo, hi):
+        v = torch.randint(lo, hi, (n_probe,), generator=gp, device=device, dtype=torch.int64)
+        return torch.stack([v, v >> 63], dim=1).contiguous()
+    return (bkeys, odate, oprio), (pk, dec(90000, 10495001), dec(0, 11))
+
+
+def run_join(args):
+    """--workload join: HashJoinExec build + probe (Inner, CollectLeft / broadcast build) on the Q3-shaped join."""
+    import torch
+    import torch.distributed as dist
+    import datafusion_upstream_b200 as df
+    import oracle
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group(backend="gloo")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    from datafusion_upstream_b200.dist import bootstrap_nccl_id, shard_range
+    uid = bootstrap_nccl_id(dist, df.GpuContext.nccl_unique_id) if world > 1 else None
+    ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+    B, P = 1_460_000, args.rows
+    bt, pt = gen_join(B, P, 42, device, rank, world)
+    bs = pa.schema([("o_orderkey", pa.int64()), ("o_orderdate", pa.date32()), ("o_shippriority", pa.int32())])
+    ps = pa.schema([("l_orderkey", pa.int64()), ("l_extendedprice", pa.decimal128(15, 2)), ("l_discount", pa.decimal128(15, 2))])
+    lo, hi = shard_range(B, rank, world)           # every rank holds a row range of the build side; it is all-gathered per step
+    bfull = df.DeviceBatch.from_device(ctx, bs, [{"buffers": [None, t.data_ptr()]} for t in bt], B, keep=bt)
+    bdev = bfull.slice(lo, hi - lo)
+    pdev = df.DeviceBatch.from_device(ctx, ps, [{"buffers": [None, t.data_ptr()]} for t in pt], P, keep=pt)
+    host_b = [(f.name, f.type, t[lo:hi]) for f, t in zip(bs, bt)]
+    host_p = [(f.name, f.type, t) for f, t in zip(ps, pt)]
+    hold = []
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def step(b, p, to_host=False):
+        j = df.GpuHashJoinExec(ctx, bs, ps, [("o_orderkey", "l_orderkey")], df.JoinType.Inner, df.PartitionMode.CollectLeft)
+        bb = b if isinstance(b, df.DeviceBatch) else df.DeviceBatch.from_arrow(ctx, b)
+        if world > 1:
+            bb = df.all_gather(ctx, bs, bb)        # broadcast build (SURVEY 8e): the probe side never moves
+        j.build([bb])
+        out = j.probe(p) if to_host else j.probe_device(p)
+        hold[:] = [(j, bb, out)]
+        return out
+
+    for _ in range(args.warmup):
+        out = step(bdev, pdev)
+    barrier()
+    ctx.set_profiling(True)
+    l0 = ctx.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clk = Clocks(local, args.clocks)
+    with clk:
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            out = step(bdev, pdev)
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    out_rows = out.num_rows
+    launches = ctx.kernel_launches - l0
+    prof = ctx.profile()
+    ctx.set_profiling(False)
+    hold.clear()
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        ot = torch.tensor([out_rows], dtype=torch.int64)
+        dist.all_reduce(ot)
+        out_rows = int(ot[0])
+    ms_per_step = ms / args.steps
+    rows_in = B + P * world
+    value = rows_in / (ms_per_step * 1e-3)
+    algo = B * 16 + P * world * 40 + out_rows * 56
+    e2e = None
+    if not args.no_e2e:
+        hb, keep_b, h2d_b = pinned_batch(ctx, bs, host_b, hi - lo, torch)
+        hp, keep_p, h2d_p = pinned_batch(ctx, ps, host_p, P, torch)
+        n_e2e = max(1, min(args.steps, 5))
+        step(hb, hp, True)
+        hold.clear()
+        barrier()
+        t0 = time.perf_counter()
+        res = None
+        for _ in range(n_e2e):
+            res = None
+            hold.clear()
+            res = step(hb, hp, True)
+        barrier()
+        dt = (time.perf_counter() - t0) / n_e2e
+        h2d, d2h = h2d_b + h2d_p, int(res.nbytes)
+        hold.clear()
+        if world > 1:
+            t = torch.tensor([dt, float(h2d), float(d2h)], dtype=torch.float64)
+            tm = t.clone()
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t)
+            dt, h2d, d2h = float(tm[0]), int(t[1]), int(t[2])
+        e2e = {"value": rows_in / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3}
+        del hb, hp, res
+        for p_ in keep_b + keep_p:
+            ctx.host_free(p_)
+    peak, peak_src = peaks()
+    roof = None
+    if prof:
+        top = max(prof, key=lambda r: r["ms"])
+        per = top["ms"] / top["launches"]
+        ach = top["algo_bytes"] / top["launches"] / (per * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": top["name"], "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                "traffic": None, "peak_source": peak_src, "launches_per_step": top["launches"] / args.steps, "ms_per_launch": round(per, 4),
+                "kernel_share_of_step": round(top["ms"] / ms, 3), "kernels": {r["name"]: round(r["ms"] / args.steps, 4) for r in prof}}
+    cpu = None
+    if rank == 0 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        sample = min(P, args.cpu_sample)
+        secs, r_, _ = oracle.bench_join_i64(bt[0].cpu().numpy(), pt[0][:sample].cpu().numpy(), threads)
+        cpu = {"value": (B + sample) / secs, "unit": "rows/s", "cores": threads, "kind": "port",
+               "sample": f"build {B} + first {sample} probe keys (Int64 keys only), P={threads} Partitioned hash joins, 8192-row batches"}
+    if rank == 0:
+        print(json.dumps({
+            "metric": "input rows/s (hash join build+probe, device-resident input) and HBM GB/s", "value": value, "unit": "rows/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+            "config": {"workload": f"TPC-H Q3-shaped join #2 at SF10 (post-filter): build {B} x 16 B, probe {P} x 40 B per GPU, Inner, "
+                                   f"{'CollectLeft' if world == 1 else 'broadcast build (NCCL all-gather)'} (BASELINE configs[2])",
+                       "build_rows": B, "probe_rows_per_gpu": P, "output_rows": out_rows, "l2_policy": "inputs larger than L2 (no flush needed)"},
+            "algorithmic_GBps": algo / (ms_per_step * 1e-3) / 1e9, "algorithmic_frac_of_peak": algo / world / (ms_per_step * 1e-3) / 1e9 / peak,
+            "clocks": clk.result, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu}))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def run_reference(args):
     """The reference's own CPU implementation of the path, on the box's host cores.  The reference is
     Rust and cannot be built here (no cargo/rustc, crates not vendored: DESIGN.md), so this arm times
@@ -459,7 +618,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--workload", default="c2", choices=["c2", "q1"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "q1", "join"])
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=50_000_000)
     ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
@@ -467,11 +626,13 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.rows <= 0:
-        args.rows = 100_000_000 if args.workload == "c2" else 60_012_150
+        args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000}[args.workload]
     if args.warmup < 3 and args.impl != "reference":
         args.warmup = max(args.warmup, 3)       # timing rules: W >= 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "join":
+        run_join(args)
     else:
         run_ours(args)
 

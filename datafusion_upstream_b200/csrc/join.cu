@@ -284,17 +284,27 @@ Batch *join_probe(JoinOp &j, const Batch &probe) {
     }
     BufRef counts = make_buf(ctx, (size_t)np * 8 + 16), offs = make_buf(ctx, (size_t)np * 8 + 16);
     const uint64_t *span = have_table ? j.span->as<uint64_t>() : nullptr;
-    k_probe_count<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np, span, jt, counts->as<int64_t>());
+    {
+        KTimer kt(ctx, "k_probe_count", np * 12);
+        k_probe_count<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np, span, jt, counts->as<int64_t>());
+    }
     note_launch(ctx);
     int64_t total = 0;
-    exclusive_scan_i64(ctx, counts->as<int64_t>(), offs->as<int64_t>(), np, &total);
+    {
+        KTimer kt(ctx, "probe_scan", np * 16);
+        exclusive_scan_i64(ctx, counts->as<int64_t>(), offs->as<int64_t>(), np, &total);
+    }
     bool left_out = jt != DFGPU_JOIN_RIGHT_SEMI && jt != DFGPU_JOIN_RIGHT_ANTI;
     bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
     BufRef ob = make_buf(ctx, (size_t)total * 8 + 16), op = make_buf(ctx, (size_t)total * 8 + 16);
     uint8_t *visited = j.visited ? j.visited->as<uint8_t>() : nullptr;
-    k_probe_scatter<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np, span, have_table ? j.rows->as<uint32_t>() : nullptr, offs->as<int64_t>(),
-                                          jt, ob->as<int64_t>(), op->as<int64_t>(), visited);
+    {
+        KTimer kt(ctx, "k_probe_scatter", np * 12 + total * 16);
+        k_probe_scatter<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np, span, have_table ? j.rows->as<uint32_t>() : nullptr, offs->as<int64_t>(),
+                                              jt, ob->as<int64_t>(), op->as<int64_t>(), visited);
+    }
     note_launch(ctx);
+    KTimer kt_gather(ctx, "probe_gather(col_take)", total * 16);
     DF_CUDA(cudaGetLastError());
     std::unique_ptr<Batch> out(new Batch());
     out->ctx = ctx;
