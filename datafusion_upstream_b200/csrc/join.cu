@@ -13,6 +13,7 @@
 #include <chrono>
 
 #include "device.cuh"
+#include "fastagg.h"
 #include "groups.h"
 
 struct dfgpu_join {
@@ -25,6 +26,9 @@ struct dfgpu_join {
     std::unique_ptr<dfgpu_batch> build;
     std::unique_ptr<dfgpu::GroupTable> table;
     dfgpu::BufRef span, rows, visited, gid_scratch;
+    dfgpu::BufRef jtags, jslots, jside;  // probe-side index of the fused path (join_fast.inc)
+    uint64_t jgroups = 0;
+    bool fast = false;
     int64_t build_rows = 0, num_keys = 0;
     bool finished = false;
     dfgpu_metrics m;
@@ -128,6 +132,8 @@ __global__ void k_compact(const int64_t *__restrict__ counts, const int64_t *__r
         if (counts[i]) out[offs[i]] = i;
 }
 
+#include "join_fast.inc"
+
 static TypeInfo forced_nullable(TypeInfo t) {
     t.nullable = true;
     return t;
@@ -206,6 +212,79 @@ static void intern_chunks(JoinOp &j, const std::vector<ColRef> &keys, int64_t n,
     }
 }
 
+// The fused probe applies when the key image fits 64 bits and no key column needs a pre-pass
+// (per-column string ids, dictionary decode).  DFGPU_DISABLE_JOIN_INDEX=1 keeps the general path.
+static bool fast_eligible(const JoinOp &j, int64_t G) {
+    const bool off = getenv("DFGPU_DISABLE_JOIN_INDEX") && atoi(getenv("DFGPU_DISABLE_JOIN_INDEX")) != 0;
+    if (off || j.ctx->opts.force_hash_collisions) return false;
+    if (j.table->mode() != KM_U64_DIRECT && j.table->mode() != KM_U64_PACKED) return false;
+    auto lay = j.table->key_layout();
+    if ((int)lay.size() > FA_MAX_KEYCOLS || G > (1LL << 30)) return false;
+    for (size_t i = 0; i < lay.size(); i++) {
+        if (lay[i].kind == 2 || lay[i].dict) return false;
+        if (j.build_schema.fields[j.bkeys[i]].id == T_DICT || j.probe_schema.fields[j.pkeys[i]].id == T_DICT) return false;
+    }
+    return true;
+}
+
+static void build_probe_index(JoinOp &j, const TableView &tv, int64_t G) {
+    Ctx *ctx = j.ctx;
+    j.fast = fast_eligible(j, G);
+    if (!j.fast) return;
+    j.jgroups = std::max<uint64_t>(4, ((uint64_t)G * 2 + JG - 1) / JG);  // load factor <= 1/2
+    j.jtags = make_buf(ctx, j.jgroups * JG + 16);
+    j.jslots = make_buf(ctx, j.jgroups * JG * 16 + 16);
+    j.jside = make_buf(ctx, 16, true);
+    DF_CUDA(cudaMemsetAsync(j.jtags->ptr, 0, j.jgroups * JG, ctx->stream));
+    k_jidx_insert<<<grid_for(G, 256, ctx, 32), 256, 0, ctx->stream>>>(tv, G, j.span->as<uint64_t>(), j.rows->as<uint32_t>(), j.jtags->as<uint32_t>(),
+                                                                      j.jslots->as<ulonglong2>(), j.jgroups, j.jside->as<uint64_t>());
+    note_launch(ctx);
+}
+
+// fused probe: returns the (build_idx, probe_idx) pairs and their number
+static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    const int64_t np = probe.num_rows;
+    JKeys jk;
+    memset(&jk, 0, sizeof jk);
+    auto lay = j.table->key_layout();
+    jk.nkeys = (int)lay.size();
+    jk.direct = j.table->mode() == KM_U64_DIRECT;
+    jk.null_off = j.table->null_off();
+    jk.nulls_excluded = j.null_equals_null ? 0 : 1;
+    for (int k = 0; k < jk.nkeys; k++) {
+        jk.keys[k].v = probe.cols[j.pkeys[k]]->view();
+        jk.keys[k].kind = lay[k].kind; jk.keys[k].off = lay[k].off; jk.keys[k].w = lay[k].w; jk.keys[k].null_bit = lay[k].null_bit;
+    }
+    JIndexView ix{j.jtags->as<uint4>(), j.jslots->as<ulonglong2>(), j.jside->as<uint64_t>(), j.jgroups};
+    const int64_t nt = (np + JP_TILE - 1) / JP_TILE;
+    BufRef ref = make_buf(ctx, (size_t)np * 4 + 64), tot = make_buf(ctx, (size_t)nt * 8 + 16), off = make_buf(ctx, (size_t)nt * 8 + 16);
+    DevBuf total_dev(ctx, 8, true);
+    {
+        KTimer kt(ctx, "k_jp_count", np * 12);
+        if (jk.direct) k_jp_count<true><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, ref->as<uint32_t>(), tot->as<unsigned long long>());
+        else k_jp_count<false><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, ref->as<uint32_t>(), tot->as<unsigned long long>());
+    }
+    {
+        KTimer kt(ctx, "k_jp_scan", nt * 16);
+        k_jp_scan<<<1, 1024, 0, st>>>(tot->as<unsigned long long>(), nt, off->as<int64_t>(), total_dev.as<int64_t>());
+    }
+    int64_t total = 0;
+    DF_CUDA(cudaMemcpyAsync(&total, total_dev.ptr, 8, cudaMemcpyDeviceToHost, st));
+    DF_CUDA(cudaStreamSynchronize(st));
+    ob = make_buf(ctx, (size_t)total * 8 + 16);
+    op = make_buf(ctx, (size_t)total * 8 + 16);
+    {
+        KTimer kt(ctx, "k_jp_scatter", np * 4 + total * 16);
+        k_jp_scatter<<<(unsigned)nt, JP_T, 0, st>>>(ix, ref->as<uint32_t>(), np, j.join_type, off->as<int64_t>(), j.rows->as<uint32_t>(),
+                                                    ob->as<int64_t>(), op->as<int64_t>(), j.visited ? j.visited->as<uint8_t>() : nullptr);
+    }
+    note_launch(ctx, 3);
+    DF_CUDA(cudaGetLastError());
+    return total;
+}
+
 void join_build_finish(JoinOp &j) {
     Ctx *ctx = j.ctx;
     cudaStream_t st = ctx->stream;
@@ -243,6 +322,7 @@ void join_build_finish(JoinOp &j) {
             k_make_span<<<grid_for(G, 256, ctx, 32), 256, 0, st>>>(starts->as<int64_t>(), cnt->as<uint32_t>(), G, j.span->as<uint64_t>(), cnt64->as<uint32_t>());
             k_build_fill<<<grid, 256, 0, st>>>(tv, gids->as<uint32_t>(), nb, j.span->as<uint64_t>(), cnt64->as<uint32_t>(), j.rows->as<uint32_t>());
             note_launch(ctx, 3);
+            build_probe_index(j, tv, G);
         }
         note_launch(ctx);
         DF_CUDA(cudaGetLastError());
@@ -261,17 +341,12 @@ static Batch *empty_output(JoinOp &j) {
     return o.release();
 }
 
-Batch *join_probe(JoinOp &j, const Batch &probe) {
+// general probe: intern the probe keys against the GroupTable (any key shape), then count -> scan -> scatter
+static int64_t probe_pairs_general(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op) {
     Ctx *ctx = j.ctx;
     cudaStream_t st = ctx->stream;
-    auto t0 = std::chrono::steady_clock::now();
-    if (!j.finished) fail(DFGPU_INTERNAL, "probe before build_finish");
-    if (probe.cols.size() != j.probe_schema.fields.size()) fail(DFGPU_INTERNAL, "probe batch does not match the probe schema");
-    int64_t np = probe.num_rows;
-    j.m.input_batches += 1;
-    j.m.input_rows += np;
-    int jt = j.join_type;
-    if (np == 0) return empty_output(j);
+    const int64_t np = probe.num_rows;
+    const int jt = j.join_type;
     BufRef gids = make_buf(ctx, (size_t)np * 4 + 16);
     int grid = grid_for(np, 256, ctx, 32);
     bool have_table = j.build_rows > 0 && j.num_keys > 0;
@@ -294,9 +369,8 @@ Batch *join_probe(JoinOp &j, const Batch &probe) {
         KTimer kt(ctx, "probe_scan", np * 16);
         exclusive_scan_i64(ctx, counts->as<int64_t>(), offs->as<int64_t>(), np, &total);
     }
-    bool left_out = jt != DFGPU_JOIN_RIGHT_SEMI && jt != DFGPU_JOIN_RIGHT_ANTI;
-    bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
-    BufRef ob = make_buf(ctx, (size_t)total * 8 + 16), op = make_buf(ctx, (size_t)total * 8 + 16);
+    ob = make_buf(ctx, (size_t)total * 8 + 16);
+    op = make_buf(ctx, (size_t)total * 8 + 16);
     uint8_t *visited = j.visited ? j.visited->as<uint8_t>() : nullptr;
     {
         KTimer kt(ctx, "k_probe_scatter", np * 12 + total * 16);
@@ -304,6 +378,28 @@ Batch *join_probe(JoinOp &j, const Batch &probe) {
                                               jt, ob->as<int64_t>(), op->as<int64_t>(), visited);
     }
     note_launch(ctx);
+    return total;
+}
+
+Batch *join_probe(JoinOp &j, const Batch &probe) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    auto t0 = std::chrono::steady_clock::now();
+    if (!j.finished) fail(DFGPU_INTERNAL, "probe before build_finish");
+    if (probe.cols.size() != j.probe_schema.fields.size()) fail(DFGPU_INTERNAL, "probe batch does not match the probe schema");
+    int64_t np = probe.num_rows;
+    j.m.input_batches += 1;
+    j.m.input_rows += np;
+    int jt = j.join_type;
+    if (np == 0) return empty_output(j);
+    bool left_out = jt != DFGPU_JOIN_RIGHT_SEMI && jt != DFGPU_JOIN_RIGHT_ANTI;
+    bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
+    BufRef ob, op;
+    int64_t total = 0;
+    bool probe_plain = true;
+    for (int c : j.pkeys) probe_plain = probe_plain && probe.cols[c]->type.id != T_DICT;
+    if (j.fast && probe_plain) total = probe_pairs_fast(j, probe, ob, op);
+    else total = probe_pairs_general(j, probe, ob, op);
     KTimer kt_gather(ctx, "probe_gather(col_take)", total * 16);
     DF_CUDA(cudaGetLastError());
     std::unique_ptr<Batch> out(new Batch());

@@ -27,6 +27,17 @@ def ctx():
     c.close()
 
 
+@pytest.fixture(autouse=True, params=["index", "general"])
+def probe_path(request, monkeypatch):
+    """Every case runs through both probe paths: the fused probe-side index (64-bit key images, join_fast.inc)
+    and the general GroupTable path it falls back to for wide / string / dictionary keys."""
+    if request.param == "general":
+        monkeypatch.setenv("DFGPU_DISABLE_JOIN_INDEX", "1")
+    else:
+        monkeypatch.delenv("DFGPU_DISABLE_JOIN_INDEX", raising=False)
+    return request.param
+
+
 def gpu_join(ctx, jt, left, right, on, null_equals_null=False, left_schema=None, right_schema=None):
     import datafusion_upstream_b200 as df
     ls = left_schema or left[0].schema
@@ -123,6 +134,26 @@ def test_join_q3_shape_large(ctx):
     want = oracle.hash_join("inner", [orders], [line], [(0, 0)])
     assert got.num_rows == want.num_rows == int(np.isin(lkey, okey).sum())
     assert_rows_equal(rows_of(got), rows_of(want))
+
+
+@pytest.mark.parametrize("jt", ALL_TYPES)
+@pytest.mark.parametrize("n_probe", [1, 1023, 1024, 1025, 2047, 2048, 2049, 3 * 2048 + 5])
+def test_join_index_edges(ctx, jt, n_probe):
+    """Fused-probe edge cases: tile boundaries (1024 rows per CTA), build keys with 1 / many rows, the key whose
+    image is all ones (-1) and, under null_equals_null, the NULL key of a single 8-byte column (both live in
+    side entries of the index)."""
+    rng = np.random.default_rng(n_probe)
+    bk = np.concatenate([np.arange(40), np.repeat([3, 7, -1], [5, 300, 2]), [2**63 - 1, -2**63]]).astype(np.int64)
+    bmask = np.zeros(len(bk), bool)
+    bmask[[1, 50]] = True
+    left = [pa.record_batch([pa.array(bk, pa.int64(), mask=bmask), pa.array(np.arange(len(bk)), pa.int32())], names=["a", "x"])]
+    pk = rng.choice(np.array([-1, 3, 7, 11, 39, 40, 999, 2**63 - 1, -2**63], dtype=np.int64), n_probe)
+    pmask = rng.random(n_probe) < 0.1
+    right = [pa.record_batch([pa.array(pk, pa.int64(), mask=pmask), pa.array(np.arange(n_probe), pa.int64())], names=["b", "y"])]
+    for nen in (False, True):
+        out, _ = gpu_join(ctx, jt, left, right, [(0, 0)], null_equals_null=nen)
+        want = oracle.hash_join(jt, left, right, [(0, 0)], null_equals_null=nen)
+        assert_rows_equal(rows_of(out), rows_of(want), what=f"{jt} n={n_probe} null_equals_null={nen}")
 
 
 def test_join_errors(ctx):
