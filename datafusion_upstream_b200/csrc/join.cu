@@ -237,7 +237,7 @@ static void build_probe_index(JoinOp &j, const TableView &tv, int64_t G) {
     j.jside = make_buf(ctx, 16, true);
     DF_CUDA(cudaMemsetAsync(j.jtags->ptr, 0, j.jgroups * JG, ctx->stream));
     k_jidx_insert<<<grid_for(G, 256, ctx, 32), 256, 0, ctx->stream>>>(tv, G, j.span->as<uint64_t>(), j.rows->as<uint32_t>(), j.jtags->as<uint32_t>(),
-                                                                      j.jslots->as<ulonglong2>(), j.jgroups, j.jside->as<uint64_t>());
+                                                                      j.jslots->as<ulonglong2>(), (uint32_t)j.jgroups, j.jside->as<uint64_t>());
     note_launch(ctx);
 }
 
