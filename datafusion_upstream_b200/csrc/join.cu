@@ -259,12 +259,18 @@ static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRe
     }
     JIndexView ix{j.jtags->as<uint4>(), j.jslots->as<ulonglong2>(), j.jside->as<uint64_t>(), j.jgroups};
     const int64_t nt = (np + JP_TILE - 1) / JP_TILE;
-    BufRef ref = make_buf(ctx, (size_t)np * 4 + 64), tot = make_buf(ctx, (size_t)nt * 8 + 16), off = make_buf(ctx, (size_t)nt * 8 + 16);
+    // per-tile emit lists live at the tile's own row range, so they need no offsets of their own
+    BufRef lsp = make_buf(ctx, (size_t)nt * JP_TILE * 8 + 16), lrow = make_buf(ctx, (size_t)nt * JP_TILE * 2 + 16);
+    BufRef tot = make_buf(ctx, (size_t)nt * 8 + 16), tne = make_buf(ctx, (size_t)nt * 4 + 16), off = make_buf(ctx, (size_t)nt * 8 + 16);
     DevBuf total_dev(ctx, 8, true);
     {
-        KTimer kt(ctx, "k_jp_count", np * 12);
-        if (jk.direct) k_jp_count<true><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, ref->as<uint32_t>(), tot->as<unsigned long long>());
-        else k_jp_count<false><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, ref->as<uint32_t>(), tot->as<unsigned long long>());
+        KTimer kt(ctx, "k_jp_count", np * 8);
+        if (jk.direct)
+            k_jp_count<true><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
+                                                            tot->as<unsigned long long>());
+        else
+            k_jp_count<false><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
+                                                             tot->as<unsigned long long>());
     }
     {
         KTimer kt(ctx, "k_jp_scan", nt * 16);
@@ -276,9 +282,10 @@ static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRe
     ob = make_buf(ctx, (size_t)total * 8 + 16);
     op = make_buf(ctx, (size_t)total * 8 + 16);
     {
-        KTimer kt(ctx, "k_jp_scatter", np * 4 + total * 16);
-        k_jp_scatter<<<(unsigned)nt, JP_T, 0, st>>>(ix, ref->as<uint32_t>(), np, j.join_type, off->as<int64_t>(), j.rows->as<uint32_t>(),
-                                                    ob->as<int64_t>(), op->as<int64_t>(), j.visited ? j.visited->as<uint8_t>() : nullptr);
+        KTimer kt(ctx, "k_jp_emit", total * 28);
+        k_jp_emit<<<(unsigned)nt, JE_T, 0, st>>>(lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(), off->as<int64_t>(), j.join_type,
+                                                 j.rows->as<uint32_t>(), ob->as<int64_t>(), op->as<int64_t>(),
+                                                 j.visited ? j.visited->as<uint8_t>() : nullptr);
     }
     note_launch(ctx, 3);
     DF_CUDA(cudaGetLastError());
