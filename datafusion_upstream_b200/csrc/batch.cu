@@ -959,6 +959,88 @@ ColRef col_take(Ctx *ctx, const DevCol &src, const int64_t *idx, int64_t n, bool
     return c;
 }
 
+// ---- take of several columns in one launch ----------------------------------------------------------
+// build_batch_from_indices (joins/utils.rs:1180-1230) gathers every output column with the same one
+// or two index arrays.  Fixed-width columns without NULLs (on either side of the gather) are taken
+// together: the indices are read once per row and the row's gathers are all in flight at once.
+static const int TAKE_MAXCOLS = 12;
+struct TakeCol {
+    const uint8_t *src;
+    uint8_t *dst;
+    const int64_t *idx;
+    int32_t w, pad;
+};
+struct TakePlan {
+    TakeCol c[TAKE_MAXCOLS];
+    int32_t n, pad;
+};
+DF_D uint4 take_load(const uint8_t *src, int w, int64_t j) {
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (w == 16) v = *(const uint4 *)(src + 16 * j);
+    else if (w == 8) { const uint2 t = *(const uint2 *)(src + 8 * j); v.x = t.x; v.y = t.y; }
+    else if (w == 4) v.x = *(const uint32_t *)(src + 4 * j);
+    else if (w == 2) v.x = *(const uint16_t *)(src + 2 * j);
+    else v.x = src[j];
+    return v;
+}
+DF_D void take_store(uint8_t *dst, int w, int64_t i, const uint4 &v) {
+    if (w == 16) *(uint4 *)(dst + 16 * i) = v;
+    else if (w == 8) *(uint2 *)(dst + 8 * i) = make_uint2(v.x, v.y);
+    else if (w == 4) *(uint32_t *)(dst + 4 * i) = v.x;
+    else if (w == 2) *(uint16_t *)(dst + 2 * i) = (uint16_t)v.x;
+    else dst[i] = (uint8_t)v.x;
+}
+__global__ void __launch_bounds__(256) k_take_multi(const __grid_constant__ TakePlan p, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        for (int c0 = 0; c0 < p.n; c0 += 4) {
+            uint4 v[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (c0 + q < p.n) v[q] = take_load(p.c[c0 + q].src, p.c[c0 + q].w, p.c[c0 + q].idx[i]);
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (c0 + q < p.n) take_store(p.c[c0 + q].dst, p.c[c0 + q].w, i, v[q]);
+        }
+    }
+}
+
+std::vector<ColRef> cols_take(Ctx *ctx, const std::vector<const DevCol *> &srcs, const std::vector<const int64_t *> &idx, int64_t n,
+                              const std::vector<bool> &idx_may_be_null) {
+    std::vector<ColRef> out(srcs.size());
+    TakePlan p;
+    memset(&p, 0, sizeof p);
+    auto flush = [&]() {
+        if (!p.n) return;
+        k_take_multi<<<grid_for(n, 256, ctx, 16), 256, 0, ctx->stream>>>(p, n);
+        note_launch(ctx);
+        p.n = 0;
+    };
+    for (size_t k = 0; k < srcs.size(); k++) {
+        const DevCol &src = *srcs[k];
+        const int32_t phys = src.type.id == T_DICT ? src.type.index_id : src.type.id;
+        const int w = type_width(phys);
+        const bool plain = n > 0 && w > 0 && phys != T_BOOL && !idx_may_be_null[k] && !(src.validity && src.null_count != 0);
+        if (!plain) {
+            out[k] = col_take(ctx, src, idx[k], n, idx_may_be_null[k]);
+            continue;
+        }
+        auto c = std::make_shared<DevCol>();
+        c->type = src.type;
+        c->length = n;
+        BufRef b = make_buf(ctx, (size_t)(n * w) + 16);
+        c->owned.push_back(b);
+        c->values = b->ptr;
+        c->dict = src.dict;
+        p.c[p.n++] = TakeCol{(const uint8_t *)src.values, b->as<uint8_t>(), idx[k], w, 0};
+        out[k] = c;
+        if (p.n == TAKE_MAXCOLS) flush();
+    }
+    flush();
+    DF_CUDA(cudaGetLastError());
+    return out;
+}
+
 __global__ void k_dict_to_idx(ColView sv, ColView dv, int64_t n, int64_t *idx) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {

@@ -256,6 +256,9 @@ Batch *batch_concat(Ctx *ctx, Batch *const *batches, int n);
 Batch *batch_slice(Ctx *ctx, const Batch *b, int64_t off, int64_t len);
 // gather rows (compute::take); idx < 0 => NULL row.  idx is a device array of n int64.
 ColRef col_take(Ctx *ctx, const DevCol &src, const int64_t *idx, int64_t n, bool idx_may_be_null);
+// the same for several columns (each with its own index array): plain fixed-width columns share one launch
+std::vector<ColRef> cols_take(Ctx *ctx, const std::vector<const DevCol *> &srcs, const std::vector<const int64_t *> &idx, int64_t n,
+                              const std::vector<bool> &idx_may_be_null);
 ColRef col_nulls(Ctx *ctx, const TypeInfo &t, int64_t n);
 ColRef col_decode_dictionary(Ctx *ctx, const DevCol &src);  // Dictionary -> plain value type
 int64_t count_nulls(Ctx *ctx, const uint8_t *validity, int64_t vbit, int64_t n);

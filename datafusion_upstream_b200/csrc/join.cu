@@ -26,7 +26,7 @@ struct dfgpu_join {
     std::unique_ptr<dfgpu_batch> build;
     std::unique_ptr<dfgpu::GroupTable> table;
     dfgpu::BufRef span, rows, visited, gid_scratch;
-    dfgpu::BufRef jtags, jslots, jside;  // probe-side index of the fused path (join_fast.inc)
+    dfgpu::BufRef jtags, jslots;  // probe-side index of the fused path (join_fast.inc)
     uint64_t jgroups = 0;
     bool fast = false;
     int64_t build_rows = 0, num_keys = 0;
@@ -212,40 +212,20 @@ static void intern_chunks(JoinOp &j, const std::vector<ColRef> &keys, int64_t n,
     }
 }
 
-// The fused probe applies when the key image fits 64 bits and no key column needs a pre-pass
-// (per-column string ids, dictionary decode).  DFGPU_DISABLE_JOIN_INDEX=1 keeps the general path.
-static bool fast_eligible(const JoinOp &j, int64_t G) {
+// The fused path applies when the key image fits 64 bits and no key column needs a pre-pass
+// (per-column string ids).  DFGPU_DISABLE_JOIN_INDEX=1 keeps the general path.
+static bool fast_eligible(const JoinOp &j, int64_t nb) {
     const bool off = getenv("DFGPU_DISABLE_JOIN_INDEX") && atoi(getenv("DFGPU_DISABLE_JOIN_INDEX")) != 0;
     if (off || j.ctx->opts.force_hash_collisions) return false;
     if (j.table->mode() != KM_U64_DIRECT && j.table->mode() != KM_U64_PACKED) return false;
     auto lay = j.table->key_layout();
-    if ((int)lay.size() > FA_MAX_KEYCOLS || G > (1LL << 30)) return false;
-    for (size_t i = 0; i < lay.size(); i++) {
-        if (lay[i].kind == 2 || lay[i].dict) return false;
-        if (j.build_schema.fields[j.bkeys[i]].id == T_DICT || j.probe_schema.fields[j.pkeys[i]].id == T_DICT) return false;
-    }
+    if ((int)lay.size() > FA_MAX_KEYCOLS || nb > (1LL << 30)) return false;
+    for (size_t i = 0; i < lay.size(); i++)
+        if (lay[i].kind == 2) return false;
     return true;
 }
 
-static void build_probe_index(JoinOp &j, const TableView &tv, int64_t G) {
-    Ctx *ctx = j.ctx;
-    j.fast = fast_eligible(j, G);
-    if (!j.fast) return;
-    j.jgroups = std::max<uint64_t>(4, ((uint64_t)G * 2 + JG - 1) / JG);  // load factor <= 1/2
-    j.jtags = make_buf(ctx, j.jgroups * JG + 16);
-    j.jslots = make_buf(ctx, j.jgroups * JG * 16 + 16);
-    j.jside = make_buf(ctx, 16, true);
-    DF_CUDA(cudaMemsetAsync(j.jtags->ptr, 0, j.jgroups * JG, ctx->stream));
-    k_jidx_insert<<<grid_for(G, 256, ctx, 32), 256, 0, ctx->stream>>>(tv, G, j.span->as<uint64_t>(), j.rows->as<uint32_t>(), j.jtags->as<uint32_t>(),
-                                                                      j.jslots->as<ulonglong2>(), (uint32_t)j.jgroups, j.jside->as<uint64_t>());
-    note_launch(ctx);
-}
-
-// fused probe: returns the (build_idx, probe_idx) pairs and their number
-static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op) {
-    Ctx *ctx = j.ctx;
-    cudaStream_t st = ctx->stream;
-    const int64_t np = probe.num_rows;
+static JKeys key_plan(const JoinOp &j, const std::vector<ColRef> &keys) {
     JKeys jk;
     memset(&jk, 0, sizeof jk);
     auto lay = j.table->key_layout();
@@ -254,40 +234,90 @@ static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRe
     jk.null_off = j.table->null_off();
     jk.nulls_excluded = j.null_equals_null ? 0 : 1;
     for (int k = 0; k < jk.nkeys; k++) {
-        jk.keys[k].v = probe.cols[j.pkeys[k]]->view();
+        jk.keys[k].v = keys[k]->view();
         jk.keys[k].kind = lay[k].kind; jk.keys[k].off = lay[k].off; jk.keys[k].w = lay[k].w; jk.keys[k].null_bit = lay[k].null_bit;
     }
-    JIndexView ix{j.jtags->as<uint4>(), j.jslots->as<ulonglong2>(), j.jside->as<uint64_t>(), j.jgroups};
+    return jk;
+}
+
+// direct build of the probe index from the build rows (join_fast.inc)
+static void build_index(JoinOp &j) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    const int64_t nb = j.build_rows;
+    j.jgroups = std::max<uint64_t>(4, ((uint64_t)nb * 2 + JG - 1) / JG);  // load factor <= 1/2
+    const uint64_t nslots = j.jgroups * JG + 2;
+    j.jtags = make_buf(ctx, j.jgroups * JG + 16);
+    j.jslots = make_buf(ctx, nslots * 16 + 16);
+    BufRef bslot = make_buf(ctx, (size_t)nb * 4 + 16);
+    DevBuf flags(ctx, 16, true);  // [0] = some key repeats, [2..3] = rows[] cursor
+    DF_CUDA(cudaMemsetAsync(j.jtags->ptr, 0, j.jgroups * JG, st));
+    k_jb_init<<<grid_for((int64_t)nslots, 256, ctx, 8), 256, 0, st>>>(j.jslots->as<ulonglong2>(), nslots);
+    std::vector<ColRef> keys = key_columns(ctx, *j.build, j.bkeys);
+    JKeys jk = key_plan(j, keys);
+    const unsigned nt = (unsigned)((nb + JP_TILE - 1) / JP_TILE);
+    {
+        KTimer kt(ctx, "k_jb_insert", nb * 8);
+        if (jk.direct)
+            k_jb_insert<true><<<nt, JP_T, 0, st>>>(jk, nb, (uint32_t)j.jgroups, j.jtags->as<uint32_t>(), j.jslots->as<ulonglong2>(), bslot->as<uint32_t>(),
+                                                   flags.as<uint32_t>());
+        else
+            k_jb_insert<false><<<nt, JP_T, 0, st>>>(jk, nb, (uint32_t)j.jgroups, j.jtags->as<uint32_t>(), j.jslots->as<ulonglong2>(), bslot->as<uint32_t>(),
+                                                    flags.as<uint32_t>());
+    }
+    note_launch(ctx, 2);
+    uint32_t dups = 0;
+    DF_CUDA(cudaMemcpyAsync(&dups, flags.ptr, 4, cudaMemcpyDeviceToHost, st));
+    DF_CUDA(cudaStreamSynchronize(st));
+    j.rows = make_buf(ctx, (dups ? (size_t)nb * 4 : 0) + 16);
+    if (dups) {
+        BufRef fill = make_buf(ctx, nslots * 4 + 16, true);
+        k_jb_starts<<<grid_for((int64_t)nslots, 256, ctx, 8), 256, 0, st>>>(j.jslots->as<ulonglong2>(), nslots, flags.as<unsigned long long>() + 1);
+        k_jb_fill<<<grid_for(nb, 256, ctx, 16), 256, 0, st>>>(j.jslots->as<ulonglong2>(), bslot->as<uint32_t>(), nb, fill->as<uint32_t>(),
+                                                             j.rows->as<uint32_t>());
+        note_launch(ctx, 2);
+    }
+    DF_CUDA(cudaGetLastError());
+}
+
+// fused probe: returns the (build_idx, probe_idx) pairs and their number
+static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    const int64_t np = probe.num_rows;
+    std::vector<ColRef> keys = key_columns(ctx, probe, j.pkeys);  // dictionary keys are decoded to plain values
+    JKeys jk = key_plan(j, keys);
+    JIndexView ix{j.jtags->as<uint4>(), j.jslots->as<ulonglong2>(), j.jgroups};
     const int64_t nt = (np + JP_TILE - 1) / JP_TILE;
     // per-tile emit lists live at the tile's own row range, so they need no offsets of their own
     BufRef lsp = make_buf(ctx, (size_t)nt * JP_TILE * 8 + 16), lrow = make_buf(ctx, (size_t)nt * JP_TILE * 2 + 16);
-    BufRef tot = make_buf(ctx, (size_t)nt * 8 + 16), tne = make_buf(ctx, (size_t)nt * 4 + 16), off = make_buf(ctx, (size_t)nt * 8 + 16);
-    DevBuf total_dev(ctx, 8, true);
+    const int64_t nsup = (nt + JP_SUPER - 1) / JP_SUPER;
+    BufRef tot = make_buf(ctx, (size_t)nt * 8 + 16), tne = make_buf(ctx, (size_t)nt * 4 + 16), sup = make_buf(ctx, (size_t)nsup * 8 + 16, true);
     {
         KTimer kt(ctx, "k_jp_count", np * 8);
         if (jk.direct)
             k_jp_count<true><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
-                                                            tot->as<unsigned long long>());
+                                                            tot->as<unsigned long long>(), sup->as<unsigned long long>());
         else
             k_jp_count<false><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
-                                                             tot->as<unsigned long long>());
+                                                             tot->as<unsigned long long>(), sup->as<unsigned long long>());
     }
-    {
-        KTimer kt(ctx, "k_jp_scan", nt * 16);
-        k_jp_scan<<<1, 1024, 0, st>>>(tot->as<unsigned long long>(), nt, off->as<int64_t>(), total_dev.as<int64_t>());
-    }
-    int64_t total = 0;
-    DF_CUDA(cudaMemcpyAsync(&total, total_dev.ptr, 8, cudaMemcpyDeviceToHost, st));
+    // the output size = sum of the super-tile sums (a few KB): summed on the host
+    std::vector<unsigned long long> hsup((size_t)nsup);
+    DF_CUDA(cudaMemcpyAsync(hsup.data(), sup->ptr, (size_t)nsup * 8, cudaMemcpyDeviceToHost, st));
     DF_CUDA(cudaStreamSynchronize(st));
+    int64_t total = 0;
+    for (auto v : hsup) total += (int64_t)v;
     ob = make_buf(ctx, (size_t)total * 8 + 16);
     op = make_buf(ctx, (size_t)total * 8 + 16);
     {
         KTimer kt(ctx, "k_jp_emit", total * 28);
-        k_jp_emit<<<(unsigned)nt, JE_T, 0, st>>>(lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(), off->as<int64_t>(), j.join_type,
+        k_jp_emit<<<(unsigned)nt, JE_T, 0, st>>>(lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(), tot->as<unsigned long long>(),
+                                                 sup->as<unsigned long long>(), j.join_type,
                                                  j.rows->as<uint32_t>(), ob->as<int64_t>(), op->as<int64_t>(),
                                                  j.visited ? j.visited->as<uint8_t>() : nullptr);
     }
-    note_launch(ctx, 3);
+    note_launch(ctx, 2);
     DF_CUDA(cudaGetLastError());
     return total;
 }
@@ -310,7 +340,11 @@ void join_build_finish(JoinOp &j) {
     int64_t nb = j.build->num_rows;
     if (nb >= (1LL << 32) - 1) fail(DFGPU_RESOURCES_EXHAUSTED, "Resources exhausted: build side larger than 2^32 rows");
     j.build_rows = nb;
-    if (nb) {
+    j.fast = nb > 0 && fast_eligible(j, nb);
+    if (j.fast) {
+        build_index(j);
+        j.num_keys = 1;
+    } else if (nb) {
         BufRef gids = make_buf(ctx, (size_t)nb * 4 + 16);
         std::vector<ColRef> keys = key_columns(ctx, *j.build, j.bkeys);
         intern_chunks(j, keys, nb, gids->as<uint32_t>(), false);
@@ -329,14 +363,14 @@ void join_build_finish(JoinOp &j) {
             k_make_span<<<grid_for(G, 256, ctx, 32), 256, 0, st>>>(starts->as<int64_t>(), cnt->as<uint32_t>(), G, j.span->as<uint64_t>(), cnt64->as<uint32_t>());
             k_build_fill<<<grid, 256, 0, st>>>(tv, gids->as<uint32_t>(), nb, j.span->as<uint64_t>(), cnt64->as<uint32_t>(), j.rows->as<uint32_t>());
             note_launch(ctx, 3);
-            build_probe_index(j, tv, G);
         }
         note_launch(ctx);
         DF_CUDA(cudaGetLastError());
     }
     if (need_final(j.join_type)) j.visited = make_buf(ctx, (size_t)nb + 16, true);
     j.finished = true;
-    j.m.build_mem_used = (int64_t)(j.table->device_bytes() + (j.span ? j.span->bytes : 0) + (j.rows ? j.rows->bytes : 0));
+    j.m.build_mem_used = (int64_t)(j.table->device_bytes() + (j.span ? j.span->bytes : 0) + (j.rows ? j.rows->bytes : 0) +
+                                   (j.jslots ? j.jslots->bytes + j.jtags->bytes : 0));
     DF_CUDA(cudaStreamSynchronize(st));
     j.m.build_time_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
 }
@@ -403,9 +437,7 @@ Batch *join_probe(JoinOp &j, const Batch &probe) {
     bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
     BufRef ob, op;
     int64_t total = 0;
-    bool probe_plain = true;
-    for (int c : j.pkeys) probe_plain = probe_plain && probe.cols[c]->type.id != T_DICT;
-    if (j.fast && probe_plain) total = probe_pairs_fast(j, probe, ob, op);
+    if (j.fast) total = probe_pairs_fast(j, probe, ob, op);
     else total = probe_pairs_general(j, probe, ob, op);
     KTimer kt_gather(ctx, "probe_gather(col_take)", total * 16);
     DF_CUDA(cudaGetLastError());
@@ -417,14 +449,27 @@ Batch *join_probe(JoinOp &j, const Batch &probe) {
         out->num_rows = total;
         size_t fi = 0;
         bool build_nullable = jt == DFGPU_JOIN_RIGHT || jt == DFGPU_JOIN_FULL;
-        if (left_out)
+        if (left_out && j.build_rows == 0)
             for (auto &c : j.build->cols) {
-                ColRef t = (j.build_rows == 0) ? col_nulls(ctx, c->type, total) : col_take(ctx, *c, ob->as<int64_t>(), total, build_nullable);
+                ColRef t = col_nulls(ctx, c->type, total);
                 t->type = j.out_schema.fields[fi++];
                 out->cols.push_back(t);
             }
+        std::vector<const DevCol *> srcs;
+        std::vector<const int64_t *> idx;
+        std::vector<bool> may_null;
+        if (left_out && j.build_rows != 0)
+            for (auto &c : j.build->cols) {
+                srcs.push_back(c.get());
+                idx.push_back(ob->as<int64_t>());
+                may_null.push_back(build_nullable);
+            }
         for (auto &c : probe.cols) {
-            ColRef t = col_take(ctx, *c, op->as<int64_t>(), total, false);
+            srcs.push_back(c.get());
+            idx.push_back(op->as<int64_t>());
+            may_null.push_back(false);
+        }
+        for (auto &t : cols_take(ctx, srcs, idx, total, may_null)) {
             t->type = j.out_schema.fields[fi++];
             out->cols.push_back(t);
         }
