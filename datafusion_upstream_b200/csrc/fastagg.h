@@ -47,7 +47,10 @@ struct FaPlan {
 // register mode of level 1 (fastagg_reg.inc)
 static const int FA_G0 = 4;         // groups held in registers
 static const int FA_MAXROLES = 16;  // distinct accumulators of a launch: one warp role each
-static const int FA_RR = 4;         // rows per thread per tile
+#ifndef FA_RR_V
+#define FA_RR_V 4
+#endif
+static const int FA_RR = FA_RR_V;   // rows per thread per tile
 struct FaRegPlan {
     int32_t nacc, slabs;
     int32_t op[FA_MAXROLES];      // logical op that defines accumulator i
