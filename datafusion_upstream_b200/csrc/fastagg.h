@@ -105,6 +105,7 @@ class FastAgg {
     BufRef recs_, scalars_, hist_, side_, plan_dev_, regplan_dev_, mode_flag_;
     int64_t cap_ = 0, used_ub_ = 0;
     bool reg_mode_allowed_ = true;
+    int reg_stages_ = 4;
 };
 
 }  // namespace dfgpu
