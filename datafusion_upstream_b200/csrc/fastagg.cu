@@ -20,6 +20,7 @@ namespace dfgpu {
 static const int FA_T1 = 512;   // level-1 threads per CTA (2 CTAs / SM)
 static const int FA_R1 = 4;     // rows per thread per tile
 static const int FA_T2 = 1024;  // level-2 threads per CTA (1 CTA / SM)
+static const int FA_KMAX = 1024; // largest per-warp chunk of the record store (records)
 static const int FA_CSTRIDE = 32; // scatter cursors live 128 B apart: same-line atomics serialise in L2
 
 struct FaStore {
@@ -172,21 +173,57 @@ DF_D void reg_combine(int kind, uint64_t &lo, uint64_t &hi, uint64_t blo, uint64
 }
 
 // ---- shared-memory hash table -------------------------------------------------------------------
-// Linear probing over 64-bit key images; a key that is present always sits before the first empty
-// slot of its probe sequence (nothing is ever deleted).  Returns the slot, or -1 when the key is
-// absent and may not be inserted (occupancy limit reached / probe budget exhausted).
+// Slots are grouped in buckets of two 64-bit key images (16 bytes, read with one 128-bit load), so a
+// warp never walks a divergent probe loop slot by slot.  Nothing is ever deleted and a key is only
+// ever inserted into the first free slot of its probe order, so a key that is present sits before
+// the first empty slot of that order.
+DF_D ulonglong2 fa_ld_bucket(const uint64_t *p) {
+    ulonglong2 v;
+    asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+    return v;
+}
+// one bucket: slot of `key` (inserting it into a free slot if absent), -1 when the bucket is held by other keys
+DF_D int fa_bucket_find_insert(uint64_t *hkeys, uint32_t b, uint64_t key) {
+    const ulonglong2 kk = fa_ld_bucket(hkeys + 2 * b);
+    if (kk.x == key) return (int)(2 * b);
+    if (kk.y == key) return (int)(2 * b + 1);
+    if (kk.x == FA_EMPTY) {
+        unsigned long long old = atomicCAS((unsigned long long *)&hkeys[2 * b], (unsigned long long)FA_EMPTY, (unsigned long long)key);
+        if (old == FA_EMPTY || old == key) return (int)(2 * b);
+    }
+    if (kk.x == FA_EMPTY || kk.y == FA_EMPTY) {  // (a lost race for slot 0 may have left slot 1 free)
+        unsigned long long old = atomicCAS((unsigned long long *)&hkeys[2 * b + 1], (unsigned long long)FA_EMPTY, (unsigned long long)key);
+        if (old == FA_EMPTY || old == key) return (int)(2 * b + 1);
+    }
+    return -1;
+}
+// Level 1 (a cache of hot keys: a miss is spilled, so one bucket is all that is looked at).
+DF_D int fa_cache_find_insert(uint64_t *hkeys, int S, uint64_t key, uint64_t h) {
+    return fa_bucket_find_insert(hkeys, __umulhi((uint32_t)h, (uint32_t)(S >> 1)), key);
+}
+// Level 2 (must hold every key of the partition): linear probing over buckets.  Returns the slot,
+// or -1 when the key is absent and may not be inserted (occupancy limit reached / probe budget
+// exhausted).  occ is only maintained when the table can fill up (occ_limit != ~0).
 DF_D int fa_find_insert(uint64_t *hkeys, int S, uint64_t key, uint64_t h, int max_probe, uint32_t *occ, uint32_t occ_limit) {
-    uint32_t s = __umulhi((uint32_t)h, (uint32_t)S);
+    const uint32_t nb = (uint32_t)(S >> 1);
+    uint32_t b = __umulhi((uint32_t)h, nb);
+    const bool limited = occ_limit != 0xffffffffu;
     for (int i = 0; i < max_probe; i++) {
-        uint64_t k = *(volatile uint64_t *)&hkeys[s];
-        if (k == key) return (int)s;
-        if (k == FA_EMPTY) {
-            if (*(volatile uint32_t *)occ >= occ_limit) return -1;
-            unsigned long long old = atomicCAS((unsigned long long *)&hkeys[s], (unsigned long long)FA_EMPTY, (unsigned long long)key);
-            if (old == FA_EMPTY) { atomicAdd(occ, 1u); return (int)s; }
-            if (old == key) return (int)s;
+        ulonglong2 kk = fa_ld_bucket(hkeys + 2 * b);
+        if (kk.x == key) return (int)(2 * b);
+        if (kk.y == key) return (int)(2 * b + 1);
+        if (kk.x == FA_EMPTY || kk.y == FA_EMPTY) {
+            if (limited && *(volatile uint32_t *)occ >= occ_limit) return -1;
+            if (kk.x == FA_EMPTY) {
+                unsigned long long old = atomicCAS((unsigned long long *)&hkeys[2 * b], (unsigned long long)FA_EMPTY, (unsigned long long)key);
+                if (old == FA_EMPTY) { if (limited) atomicAdd(occ, 1u); return (int)(2 * b); }
+                if (old == key) return (int)(2 * b);
+            }
+            unsigned long long old = atomicCAS((unsigned long long *)&hkeys[2 * b + 1], (unsigned long long)FA_EMPTY, (unsigned long long)key);
+            if (old == FA_EMPTY) { if (limited) atomicAdd(occ, 1u); return (int)(2 * b + 1); }
+            if (old == key) return (int)(2 * b + 1);
         }
-        s = s + 1 == (uint32_t)S ? 0 : s + 1;
+        b = b + 1 == nb ? 0 : b + 1;
     }
     return -1;
 }
@@ -206,16 +243,20 @@ DF_D void fa_init_table(const FaPlan &pl, uint64_t *hkeys, uint64_t *hstate, int
 }
 
 // ---- level 1: per-CTA pre-aggregation + spill ---------------------------------------------------
-__global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ plan_g, int64_t n, FaStore st, int S, int max_probe,
+// The tile loop has no block-wide barrier: every warp reserves space for its spilled records in
+// private chunks of K records (one global atomic per chunk); what is left of a chunk when a tile
+// does not fit, and at the end, is filled with hole records (key image FA_EMPTY, skipped by the
+// scatter).
+__global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ plan_g, int64_t n, FaStore st, int S, int K,
                                                     const uint32_t *__restrict__ mode_flag, uint32_t my_mode) {
     if (mode_flag && *mode_flag != my_mode) return;
     extern __shared__ __align__(16) uint8_t fa_smem[];
-    __shared__ uint32_t s_cnt, s_occ, s_side[2];
+    __shared__ uint32_t s_cnt, s_side[2];
     __shared__ unsigned long long s_base;
     FaPlan &pl = *(FaPlan *)fa_smem;
     const int tid = threadIdx.x, lane = tid & 31;
     for (int i = tid; i < (int)(sizeof(FaPlan) / 4); i += FA_T1) ((uint32_t *)&pl)[i] = ((const uint32_t *)plan_g)[i];
-    if (tid == 0) { s_cnt = 0; s_occ = 0; s_side[0] = 0; s_side[1] = 0; }
+    if (tid == 0) { s_cnt = 0; s_side[0] = 0; s_side[1] = 0; }
     __syncthreads();
     const int stride = S + 2;
     const int SW = pl.SW, RW = pl.RW, nops = pl.nops;
@@ -225,8 +266,9 @@ __global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ p
     fa_init_table(pl, hkeys, hstate, S, stride, tid, FA_T1);
     for (int p = tid; p < FA_P; p += FA_T1) hist[p] = 0;
     __syncthreads();
-    const uint32_t occ_limit = (uint32_t)(S / 2);
 
+    uint64_t w_pos = 0, w_end = 0;  // this warp's current chunk of the record store (warp-uniform)
+    bool can_write = true;
     const int64_t tile_rows = (int64_t)FA_T1 * FA_R1;
     for (int64_t tile = blockIdx.x; tile * tile_rows < n; tile += gridDim.x) {
         const int64_t base = tile * tile_rows + tid;
@@ -245,33 +287,36 @@ __global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ p
                     slot[k] = S + side;
                     s_side[side] = 1;
                 } else {
-                    slot[k] = fa_find_insert(hkeys, S, key[k], fa_hash(key[k]), max_probe, &s_occ, occ_limit);
+                    slot[k] = fa_cache_find_insert(hkeys, S, key[k], fa_hash(key[k]));
                     if (slot[k] < 0) nspill++;
                 }
             }
         }
-        // reserve space for this tile's spilled records: one global atomic per CTA
+        // reserve space for this warp's spilled records
         uint64_t rec0 = 0;
-        bool can_write = true;
-        if (__syncthreads_or(nspill)) {
+        if (__any_sync(0xffffffffu, nspill)) {
             int incl = nspill;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 int t = __shfl_up_sync(0xffffffffu, incl, o);
                 if (lane >= o) incl += t;
             }
-            uint32_t wbase = 0;
-            if (lane == 31 && incl) wbase = atomicAdd(&s_cnt, (uint32_t)incl);
-            wbase = __shfl_sync(0xffffffffu, wbase, 31);
-            __syncthreads();
-            if (tid == 0) {
-                s_base = atomicAdd(st.cursor, (unsigned long long)s_cnt);
-                if (s_base + s_cnt > st.cap) atomicExch(st.err, 1u);
-                s_cnt = 0;
+            const uint64_t m = (uint64_t)__shfl_sync(0xffffffffu, incl, 31);
+            if (w_pos + m > w_end) {
+                if (can_write)
+                    for (uint64_t r = w_pos + lane; r < w_end; r += 32) st.recs[r * RW] = FA_EMPTY;
+                unsigned long long b = 0;
+                if (lane == 0) b = atomicAdd(st.cursor, (unsigned long long)K);
+                b = __shfl_sync(0xffffffffu, b, 0);
+                if (b + (uint64_t)K > st.cap) {
+                    if (lane == 0) atomicExch(st.err, 1u);
+                    can_write = false;
+                }
+                w_pos = b;
+                w_end = b + (uint64_t)K;
             }
-            __syncthreads();
-            rec0 = s_base + wbase + (uint32_t)(incl - nspill);
-            can_write = rec0 + nspill <= st.cap;
+            rec0 = w_pos + (uint64_t)(incl - nspill);
+            w_pos += m;
         }
         uint32_t seenmask[FA_R1];
 #pragma unroll
@@ -321,6 +366,8 @@ __global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ p
             }
         }
     }
+    if (can_write)  // the rest of the warp's last chunk
+        for (uint64_t r = w_pos + lane; r < w_end; r += 32) st.recs[r * RW] = FA_EMPTY;
     __syncthreads();
     // ---- flush the table as partial-state records -----------------------------------------------
     {
