@@ -19,7 +19,7 @@ namespace dfgpu {
 
 static const int FA_T1 = 512;   // level-1 threads per CTA (2 CTAs / SM)
 static const int FA_R1 = 4;     // rows per thread per tile
-static const int FA_T2 = 1024;  // level-2 threads per CTA (1 CTA / SM)
+static const int FA_T2 = 512;   // level-2 threads per CTA (2 CTAs / SM: one merges while the other initialises / emits)
 static const int FA_KMAX = 1024; // largest per-warp chunk of the record store (records)
 static const int FA_CSTRIDE = 32; // scatter cursors live 128 B apart: same-line atomics serialise in L2
 

@@ -22,7 +22,7 @@ namespace dfgpu {
 
 static const int FA_MAX_OPS = 24;
 static const int FA_MAX_KEYCOLS = 8;
-static const int FA_PBITS = 12;
+static const int FA_PBITS = 13;
 static const int FA_P = 1 << FA_PBITS;     // partitions per level
 static const uint64_t FA_EMPTY = ~0ULL;    // free-slot marker; the real key ~0 lives in side group 1
 
