@@ -11,6 +11,8 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
+#include <set>
 
 #include "device.cuh"
 #include "fastagg.h"

@@ -106,6 +106,7 @@ class FastAgg {
     int64_t cap_ = 0, used_ub_ = 0;
     bool reg_mode_allowed_ = true;
     int reg_stages_ = 4;
+    int64_t single_max_ = 8192;  // record sets up to this size are first merged by one CTA, unpartitioned
 };
 
 }  // namespace dfgpu

@@ -24,6 +24,7 @@ HOOKS = {
     "default": {},
     "tiny_tables": {"DFGPU_FA_S2MAX": "64", "DFGPU_FA_S1": "32"},    # spills at level 1, overflow rounds at level 2
     "no_register_mode": {"DFGPU_FA_NOREG": "1"},
+    "always_partition": {"DFGPU_FA_SINGLE_MAX": "0"},                 # small record sets through hist -> scan -> scatter -> level 2 too
     "table_path": {"DFGPU_DISABLE_TWO_LEVEL": "1"},                   # same specs through GroupTable + k_accumulate
 }
 
