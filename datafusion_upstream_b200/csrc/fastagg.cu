@@ -272,19 +272,35 @@ __global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ p
     uint64_t w_pos = 0, w_end = 0;  // this warp's current chunk of the record store (warp-uniform)
     bool can_write = true;
     const int64_t tile_rows = (int64_t)FA_T1 * FA_R1;
+    // a single 8-byte key column without a validity bitmap: the keys of the next tile are loaded
+    // into registers before this tile is worked on
+    const bool kdirect = pl.direct && pl.keys[0].v.validity == nullptr;
+    const uint64_t *const kvals = (const uint64_t *)pl.keys[0].v.values;
+    uint64_t nkey[FA_R1];
+    auto load_next_keys = [&](int64_t tile) {
+#pragma unroll
+        for (int k = 0; k < FA_R1; k++) {
+            const int64_t row = tile * tile_rows + tid + (int64_t)k * FA_T1;
+            nkey[k] = (kdirect && row < n) ? ld_stream_u64(kvals + row) : 0;
+        }
+    };
+    load_next_keys(blockIdx.x);
     for (int64_t tile = blockIdx.x; tile * tile_rows < n; tile += gridDim.x) {
         const int64_t base = tile * tile_rows + tid;
         uint64_t key[FA_R1];
         int slot[FA_R1];  // >= 0: table slot (S, S+1 = side groups); -1: spill; -2: past the end
         int nspill = 0;
 #pragma unroll
+        for (int k = 0; k < FA_R1; k++) key[k] = nkey[k];
+        load_next_keys(tile + gridDim.x);
+#pragma unroll
         for (int k = 0; k < FA_R1; k++) {
             int64_t row = base + (int64_t)k * FA_T1;
             slot[k] = -2;
-            key[k] = 0;
             if (row < n) {
-                int side;
-                fa_load_key(pl, row, key[k], side);
+                int side = -1;
+                if (kdirect) { if (key[k] == FA_EMPTY) side = 1; }
+                else fa_load_key(pl, row, key[k], side);
                 if (side >= 0) {
                     slot[k] = S + side;
                     s_side[side] = 1;
