@@ -364,6 +364,8 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (CUDA events recorded live by the library) ----
     peak, peak_src = peaks()
     roof = None
+    stages = {r["name"][6:]: round(r["ms"] / args.steps, 4) for r in prof if r["name"].startswith("stage:")} if prof else {}
+    prof = [r for r in prof if not r["name"].startswith("stage:")] if prof else prof
     if prof:
         top = max(prof, key=lambda r: r["ms"])
         per_launch_ms = top["ms"] / top["launches"]
@@ -376,7 +378,7 @@ def run_ours(args):
                 "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                 "launches_per_step": top["launches"] / args.steps, "ms_per_launch": round(per_launch_ms, 4),
                 "kernel_share_of_step": round(top["ms"] / ms, 3),
-                "kernels": {r["name"]: round(r["ms"] / args.steps, 4) for r in prof}}
+                "kernels": {r["name"]: round(r["ms"] / args.steps, 4) for r in prof}, "stages": stages}
     algo_bytes = w["in_bytes"] + w["out_row_bytes"] * (groups // world)
     # ---- CPU baseline (the oracle port, reference-shaped parallel plan) on rank 0 ----
     cpu = None
@@ -534,13 +536,15 @@ def run_join(args):
             ctx.host_free(p_)
     peak, peak_src = peaks()
     roof = None
+    stages = {r["name"][6:]: round(r["ms"] / args.steps, 4) for r in prof if r["name"].startswith("stage:")} if prof else {}
+    prof = [r for r in prof if not r["name"].startswith("stage:")] if prof else prof
     if prof:
         top = max(prof, key=lambda r: r["ms"])
         per = top["ms"] / top["launches"]
         ach = top["algo_bytes"] / top["launches"] / (per * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": top["name"], "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
                 "traffic": None, "peak_source": peak_src, "launches_per_step": top["launches"] / args.steps, "ms_per_launch": round(per, 4),
-                "kernel_share_of_step": round(top["ms"] / ms, 3), "kernels": {r["name"]: round(r["ms"] / args.steps, 4) for r in prof}}
+                "kernel_share_of_step": round(top["ms"] / ms, 3), "kernels": {r["name"]: round(r["ms"] / args.steps, 4) for r in prof}, "stages": stages}
     cpu = None
     if rank == 0 and not args.no_cpu:
         threads = os.cpu_count() or 1
@@ -561,6 +565,198 @@ def run_join(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def gen_q3(sf, seed, device, rank=0, world=1):
+    """Post-filter inputs of the three scans of TPC-H Q3 at scale factor `sf`, generated on the device:
+    customer (c_custkey; c_mktsegment keeps 1 in 5), orders (o_orderkey sparse 8-of-32, o_custkey, o_orderdate < 1995-03-15,
+    o_shippriority = 0), lineitem (l_orderkey, l_extendedprice, l_discount; l_shipdate = o_orderdate + 1..121 > 1995-03-15).
+    With world > 1 the lineitem rows are this rank's shard (its own seed); customer and orders are replicated."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    n_cust, n_orders, n_line = 150_000 * sf, 1_500_000 * sf, 6_000_000 * sf
+    custkey = torch.arange(1, n_cust + 1, device=device, dtype=torch.int64)
+    cust = custkey[torch.rand(n_cust, generator=g, device=device) < 0.2].contiguous()
+    ok = torch.arange(0, n_orders, device=device, dtype=torch.int64)
+    okey = (ok // 8) * 32 + (ok % 8) + 1
+    valid = custkey[custkey % 3 != 0]
+    ocust = valid[torch.randint(0, valid.numel(), (n_orders,), generator=g, device=device)]
+    odate = torch.randint(8035, 10440, (n_orders,), generator=g, device=device, dtype=torch.int32)
+    keep = odate < 9204
+    orders = (okey[keep].contiguous(), ocust[keep].contiguous(), odate[keep].contiguous(),
+              torch.zeros(int(keep.sum()), device=device, dtype=torch.int32))
+    gl = torch.Generator(device=device)
+    gl.manual_seed(seed + 1000 + rank)
+    oi = torch.randint(0, n_orders, (n_line,), generator=gl, device=device)
+    ship = odate[oi] + torch.randint(1, 122, (n_line,), generator=gl, device=device, dtype=torch.int32)
+    lkey = okey[oi][ship > 9204].contiguous()
+    n_l = lkey.numel()
+    del oi, ship
+
+    def dec(lo, hi):
+        v = torch.randint(lo, hi, (n_l,), generator=gl, device=device, dtype=torch.int64)
+        return torch.stack([v, v >> 63], dim=1).contiguous()
+    return (cust,), orders, (lkey, dec(90000, 10495001), dec(0, 11))
+
+
+def run_q3(args):
+    """--workload q3: the whole Q3-shaped operator chain (BASELINE configs[2]): join #1 customer x orders, join #2 x lineitem,
+    then GROUP BY (l_orderkey, o_orderdate, o_shippriority) SUM/COUNT - Single on one GPU, Partial -> NCCL all-to-all ->
+    FinalPartitioned when sharded (lineitem sharded, customer / orders replicated = CollectLeft builds)."""
+    import torch
+    import torch.distributed as dist
+    import datafusion_upstream_b200 as df
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group(backend="gloo")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    from datafusion_upstream_b200.dist import bootstrap_nccl_id
+    uid = bootstrap_nccl_id(dist, df.GpuContext.nccl_unique_id) if world > 1 else None
+    ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+    sf = max(1, args.rows)
+    ct, ot, lt = gen_q3(sf, 42, device, rank, world)
+    cs = pa.schema([("c_custkey", pa.int64())])
+    os_ = pa.schema([("o_orderkey", pa.int64()), ("o_custkey", pa.int64()), ("o_orderdate", pa.date32()), ("o_shippriority", pa.int32())])
+    ls = pa.schema([("l_orderkey", pa.int64()), ("l_extendedprice", pa.decimal128(15, 2)), ("l_discount", pa.decimal128(15, 2))])
+
+    def devb(schema, ts):
+        return df.DeviceBatch.from_device(ctx, schema, [{"buffers": [None, t.data_ptr()]} for t in ts], ts[0].shape[0], keep=ts)
+    cdev, odev, ldev = devb(cs, ct), devb(os_, ot), devb(ls, lt)
+    nC, nO, nL = ct[0].shape[0], ot[0].shape[0], lt[0].shape[0]
+    group = ["l_orderkey", "o_orderdate", "o_shippriority"]
+    exprs = [df.AggregateExpr(df.AggFunc.Sum, "l_extendedprice", "SUM(l_extendedprice)"), df.AggregateExpr(df.AggFunc.Sum, "l_discount", "SUM(l_discount)"),
+             df.AggregateExpr(df.AggFunc.Count, None, "COUNT(*)")]
+    hold = []
+    stats = {}
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def step(c, o, l, to_host=False):
+        j1 = df.GpuHashJoinExec(ctx, cs, os_, [("c_custkey", "o_custkey")], df.JoinType.Inner, df.PartitionMode.CollectLeft)
+        j1.build([c])
+        o1 = j1.probe_device(o).project(["o_orderkey", "o_orderdate", "o_shippriority"])
+        j2 = df.GpuHashJoinExec(ctx, o1.schema, ls, [("o_orderkey", "l_orderkey")], df.JoinType.Inner, df.PartitionMode.CollectLeft)
+        j2.build([o1])
+        jo = j2.probe_device(l).project(group + ["l_extendedprice", "l_discount"])
+        stats["j1"], stats["j2"] = o1.num_rows, jo.num_rows
+        if world == 1:
+            agg = df.GpuAggregateExec(ctx, df.AggregateMode.Single, jo.schema, group, exprs)
+            agg.push(jo)
+            out = agg.emit() if to_host else agg.emit_device()
+            hold[:] = [(j1, j2, o1, jo, agg, out)]
+            return out
+        part = df.GpuAggregateExec(ctx, df.AggregateMode.Partial, jo.schema, group, exprs)
+        part.push(jo)
+        st = part.emit_device()
+        rp = df.GpuRepartitionExec(ctx, part.schema, [0, 1, 2], world)
+        recv = rp.exchange(rp.partition_device(st))
+        fin = df.GpuAggregateExec(ctx, df.AggregateMode.FinalPartitioned, part.schema, [0, 1, 2], [df.AggregateExpr(e.func, None, e.name) for e in exprs])
+        if recv is not None:
+            fin.push(recv)
+        out = fin.emit() if to_host else fin.emit_device()
+        hold[:] = [(j1, j2, o1, jo, part, st, recv, fin, out)]
+        return out
+
+    for _ in range(args.warmup):
+        out = step(cdev, odev, ldev)
+    barrier()
+    ctx.set_profiling(True)
+    l0 = ctx.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clk = Clocks(local, args.clocks)
+    with clk:
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            out = step(cdev, odev, ldev)
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    groups = out.num_rows
+    launches = ctx.kernel_launches - l0
+    prof = ctx.profile()
+    ctx.set_profiling(False)
+    hold.clear()
+    rows_local = nC + nO + nL
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        gt = torch.tensor([groups, nL, stats["j2"]], dtype=torch.int64)
+        dist.all_reduce(gt)
+        groups, nL_all, j2_all = int(gt[0]), int(gt[1]), int(gt[2])
+    else:
+        nL_all, j2_all = nL, stats["j2"]
+    ms_per_step = ms / args.steps
+    rows_in = (nC + nO) * world + nL_all          # every rank reads its replicated build sides
+    value = rows_in / (ms_per_step * 1e-3)
+    # SURVEY 8d: consumed input columns once + output rows once, per operator
+    algo = world * (nC * 8 + nO * 24 + stats["j1"] * 16) + (world * stats["j1"] * 16 + nL_all * 40 + j2_all * 56) + (j2_all * 48 + groups * 56)
+    e2e = None
+    if not args.no_e2e:
+        hc, kc, b1 = pinned_batch(ctx, cs, [(f.name, f.type, t) for f, t in zip(cs, ct)], nC, torch)
+        ho, ko, b2 = pinned_batch(ctx, os_, [(f.name, f.type, t) for f, t in zip(os_, ot)], nO, torch)
+        hl, kl, b3 = pinned_batch(ctx, ls, [(f.name, f.type, t) for f, t in zip(ls, lt)], nL, torch)
+        n_e2e = max(1, min(args.steps, 5))
+        step(hc, ho, hl, True)
+        hold.clear()
+        barrier()
+        t0 = time.perf_counter()
+        res = None
+        for _ in range(n_e2e):
+            res = None
+            hold.clear()
+            res = step(hc, ho, hl, True)
+        barrier()
+        dt = (time.perf_counter() - t0) / n_e2e
+        h2d, d2h = b1 + b2 + b3, int(res.nbytes)
+        hold.clear()
+        if world > 1:
+            t = torch.tensor([dt, float(h2d), float(d2h)], dtype=torch.float64)
+            tm = t.clone()
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t)
+            dt, h2d, d2h = float(tm[0]), int(t[1]), int(t[2])
+        e2e = {"value": rows_in / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3}
+        del hc, ho, hl, res
+        for p_ in kc + ko + kl:
+            ctx.host_free(p_)
+    peak, peak_src = peaks()
+    roof = None
+    stages = {r["name"][6:]: round(r["ms"] / args.steps, 4) for r in prof if r["name"].startswith("stage:")} if prof else {}
+    prof = [r for r in prof if not r["name"].startswith("stage:")] if prof else prof
+    if prof:
+        top = max(prof, key=lambda r: r["ms"])
+        per = top["ms"] / top["launches"]
+        ach = top["algo_bytes"] / top["launches"] / (per * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": top["name"], "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                "traffic": None, "peak_source": peak_src, "launches_per_step": top["launches"] / args.steps, "ms_per_launch": round(per, 4),
+                "kernel_share_of_step": round(top["ms"] / ms, 3), "kernels": {r["name"]: round(r["ms"] / args.steps, 4) for r in prof}, "stages": stages}
+    if rank == 0:
+        print(json.dumps({
+            "metric": "input rows/s (Q3-shaped join + join + aggregation chain, device-resident input) and HBM GB/s", "value": value, "unit": "rows/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "i128", "data": "synthetic",
+            "config": {"workload": f"TPC-H Q3-shaped chain at SF{sf} (post-filter scans): customer {nC} x orders {nO} -> {stats['j1']} rows, x lineitem "
+                                   f"{nL} per GPU -> {j2_all} rows, GROUP BY (l_orderkey, o_orderdate, o_shippriority) -> {groups} groups (BASELINE configs[2])",
+                       "customer_rows": nC, "orders_rows": nO, "lineitem_rows_per_gpu": nL, "join1_rows": stats["j1"], "join2_rows": j2_all, "groups": groups,
+                       "l2_policy": "inputs larger than L2 (no flush needed)",
+                       "mode": "Single" if world == 1 else f"CollectLeft builds replicated, lineitem sharded, Partial -> NCCL all-to-all -> FinalPartitioned (dp{world})"},
+            "algorithmic_GBps": algo / (ms_per_step * 1e-3) / 1e9, "algorithmic_frac_of_peak": algo / world / (ms_per_step * 1e-3) / 1e9 / peak,
+            "clocks": clk.result, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": None}))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
 
 
 def run_reference(args):
@@ -618,7 +814,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--workload", default="c2", choices=["c2", "q1", "join"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "q1", "join", "q3"])
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=50_000_000)
     ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
@@ -626,13 +822,15 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.rows <= 0:
-        args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000}[args.workload]
+        args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000, "q3": 10}[args.workload]   # q3: --rows = scale factor
     if args.warmup < 3 and args.impl != "reference":
         args.warmup = max(args.warmup, 3)       # timing rules: W >= 3
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "join":
         run_join(args)
+    elif args.workload == "q3":
+        run_q3(args)
     else:
         run_ours(args)
 

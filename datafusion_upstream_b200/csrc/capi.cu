@@ -228,6 +228,18 @@ dfgpu_status dfgpu_batch_slice(dfgpu_ctx *ctx, const dfgpu_batch *b, int64_t off
     *out = batch_slice(ctx, b, off, len);
     DF_CATCH
 }
+dfgpu_status dfgpu_batch_project(dfgpu_ctx *ctx, const dfgpu_batch *b, const int32_t *cols, int32_t n_cols, dfgpu_batch **out) {
+    DF_TRY
+    std::unique_ptr<Batch> o(new Batch());
+    o->ctx = ctx;
+    o->num_rows = b->num_rows;
+    for (int i = 0; i < n_cols; i++) {
+        if (cols[i] < 0 || cols[i] >= (int)b->cols.size()) fail(DFGPU_PLAN, "project: column index out of range");
+        o->cols.push_back(b->cols[cols[i]]);
+    }
+    *out = o.release();
+    DF_CATCH
+}
 void dfgpu_batch_free(dfgpu_batch *b) {
     if (!b) return;
     cudaSetDevice(b->ctx->device);

@@ -2,6 +2,7 @@
 // (physical-plan/src/repartition/mod.rs:162-217) as a stable multi-split, and the exchange itself
 // (the reference's per-partition channels, repartition/mod.rs:442-580, distributor_channels.rs)
 // as grouped ncclSend/ncclRecv all-to-all over NVLink.
+#include <functional>
 #include <dlfcn.h>
 #include <nccl.h>
 
@@ -105,7 +106,12 @@ static BufRef partition_perm(Ctx *ctx, const Batch &b, const int32_t *key_cols, 
 
 void partition_hash(Ctx *ctx, const Batch &b, const int32_t *key_cols, int n_keys, int P, Batch **out_parts) {
     std::vector<int64_t> off;
-    BufRef perm = partition_perm(ctx, b, key_cols, n_keys, P, off);
+    BufRef perm;
+    {
+        KTimer kt(ctx, "stage:partition_perm");
+        perm = partition_perm(ctx, b, key_cols, n_keys, P, off);
+    }
+    KTimer kt(ctx, "stage:partition_take");
     for (int p = 0; p < P; p++) {
         out_parts[p] = nullptr;
         int64_t cnt = off[(size_t)p + 1] - off[(size_t)p];
@@ -277,6 +283,13 @@ Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) 
     std::unique_ptr<Batch> out(new Batch());
     out->ctx = ctx;
     out->num_rows = total;
+    // Three phases, so that the whole batch crosses NVLink in ONE grouped NCCL call (a group per
+    // column buffer costs a launch and a rendezvous each; partial-state batches have dozens):
+    //   1. per column: receive buffers, send staging (bitmap -> bytes, lengths of var-width rows);
+    //   2. every ncclSend / ncclRecv of every column inside one ncclGroupStart / ncclGroupEnd;
+    //   3. per column: rebuild validity bitmaps / offsets from what arrived.
+    std::vector<std::function<void()>> comm_ops, post_ops;
+    std::vector<std::shared_ptr<DevCol>> cols_out(nc);
     for (size_t c = 0; c < nc; c++) {
         TypeInfo ft = schema.fields[c];
         TypeInfo vt = ft.value_type();
@@ -285,13 +298,12 @@ Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) 
         for (int s = 0; s < W; s++)
             for (int d = 0; d < W; d++) any_valid = any_valid || cnt(s, d, 2 + 2 * c) != 0;
         auto col = std::make_shared<DevCol>();
+        cols_out[c] = col;
         col->type = vt;
         col->length = total;
-        std::vector<BufRef> keep;
         // 1) validity bytes
-        BufRef rv;
         if (any_valid) {
-            rv = make_buf(ctx, (size_t)total + 16);
+            BufRef rv = make_buf(ctx, (size_t)total + 16);
             std::vector<BufRef> sv((size_t)W);
             for (int r = 0; r < W; r++) {
                 int64_t n = mine[r * rec];
@@ -303,19 +315,20 @@ Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) 
                     note_launch(ctx);
                 }
             }
-            DF_NCCL(nccl().GroupStart());
-            for (int r = 0; r < W; r++) {
-                if (mine[r * rec]) DF_NCCL(nccl().Send(sv[r]->ptr, (size_t)mine[r * rec], ncclChar, r, comm, st));
-                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rv->as<uint8_t>() + row_off[r], (size_t)cnt(r, me, 0), ncclChar, r, comm, st));
-            }
-            DF_NCCL(nccl().GroupEnd());
-            for (int r = 0; r < W; r++) if (r != me) ctx->nvlink_bytes += mine[r * rec];
-            BufRef bits = make_buf(ctx, (size_t)((total + 31) / 32) * 4 + 16, true);
-            if (total) { k_bytes_to_bits<<<grid_for(total, 256, ctx, 16), 256, 0, st>>>(rv->as<uint8_t>(), total, bits->as<uint32_t>()); note_launch(ctx); }
-            col->owned.push_back(bits);
-            col->validity = bits->as<uint8_t>();
-            col->null_count = -1;
-            keep.insert(keep.end(), sv.begin(), sv.end());
+            comm_ops.push_back([=, &mine, &row_off, &cnt]() {
+                for (int r = 0; r < W; r++) {
+                    if (mine[r * rec]) DF_NCCL(nccl().Send(sv[r]->ptr, (size_t)mine[r * rec], ncclChar, r, comm, st));
+                    if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rv->as<uint8_t>() + row_off[r], (size_t)cnt(r, me, 0), ncclChar, r, comm, st));
+                    if (r != me) ctx->nvlink_bytes += mine[r * rec];
+                }
+            });
+            post_ops.push_back([=]() {
+                BufRef bits = make_buf(ctx, (size_t)((total + 31) / 32) * 4 + 16, true);
+                if (total) { k_bytes_to_bits<<<grid_for(total, 256, ctx, 16), 256, 0, st>>>(rv->as<uint8_t>(), total, bits->as<uint32_t>()); note_launch(ctx); }
+                col->owned.push_back(bits);
+                col->validity = bits->as<uint8_t>();
+                col->null_count = -1;
+            });
         }
         // 2) payload
         int w = vt.width();
@@ -327,27 +340,29 @@ Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) 
                 sb[r] = make_buf(ctx, (size_t)n + 16);
                 if (n) { k_bitmap_to_bytes<<<grid_for(n, 256, ctx, 16), 256, 0, st>>>((const uint8_t *)send[r][c]->values, send[r][c]->dbit, n, sb[r]->as<uint8_t>(), 0); note_launch(ctx); }
             }
-            DF_NCCL(nccl().GroupStart());
-            for (int r = 0; r < W; r++) {
-                if (mine[r * rec]) DF_NCCL(nccl().Send(sb[r]->ptr, (size_t)mine[r * rec], ncclChar, r, comm, st));
-                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rb->as<uint8_t>() + row_off[r], (size_t)cnt(r, me, 0), ncclChar, r, comm, st));
-            }
-            DF_NCCL(nccl().GroupEnd());
-            BufRef bits = make_buf(ctx, (size_t)((total + 31) / 32) * 4 + 16, true);
-            if (total) { k_bytes_to_bits<<<grid_for(total, 256, ctx, 16), 256, 0, st>>>(rb->as<uint8_t>(), total, bits->as<uint32_t>()); note_launch(ctx); }
-            col->owned.push_back(bits);
-            col->values = bits->ptr;
-            keep.insert(keep.end(), sb.begin(), sb.end());
-            keep.push_back(rb);
+            comm_ops.push_back([=, &mine, &row_off, &cnt]() {
+                for (int r = 0; r < W; r++) {
+                    if (mine[r * rec]) DF_NCCL(nccl().Send(sb[r]->ptr, (size_t)mine[r * rec], ncclChar, r, comm, st));
+                    if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rb->as<uint8_t>() + row_off[r], (size_t)cnt(r, me, 0), ncclChar, r, comm, st));
+                    if (r != me) ctx->nvlink_bytes += mine[r * rec];
+                }
+            });
+            post_ops.push_back([=]() {
+                BufRef bits = make_buf(ctx, (size_t)((total + 31) / 32) * 4 + 16, true);
+                if (total) { k_bytes_to_bits<<<grid_for(total, 256, ctx, 16), 256, 0, st>>>(rb->as<uint8_t>(), total, bits->as<uint32_t>()); note_launch(ctx); }
+                col->owned.push_back(bits);
+                col->values = bits->ptr;
+            });
         } else if (w > 0) {
             BufRef rb = make_buf(ctx, (size_t)total * w + 16);
-            DF_NCCL(nccl().GroupStart());
-            for (int r = 0; r < W; r++) {
-                if (mine[r * rec]) DF_NCCL(nccl().Send(send[r][c]->values, (size_t)mine[r * rec] * w, ncclChar, r, comm, st));
-                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rb->as<uint8_t>() + row_off[r] * w, (size_t)cnt(r, me, 0) * w, ncclChar, r, comm, st));
-            }
-            DF_NCCL(nccl().GroupEnd());
-            for (int r = 0; r < W; r++) if (r != me) ctx->nvlink_bytes += mine[r * rec] * w;
+            const std::vector<ColRef> *sendp = send.data();
+            comm_ops.push_back([=, &mine, &row_off, &cnt]() {
+                for (int r = 0; r < W; r++) {
+                    if (mine[r * rec]) DF_NCCL(nccl().Send(sendp[r][c]->values, (size_t)mine[r * rec] * w, ncclChar, r, comm, st));
+                    if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rb->as<uint8_t>() + row_off[r] * w, (size_t)cnt(r, me, 0) * w, ncclChar, r, comm, st));
+                    if (r != me) ctx->nvlink_bytes += mine[r * rec] * w;
+                }
+            });
             col->owned.push_back(rb);
             col->values = rb->ptr;
         } else {
@@ -371,37 +386,49 @@ Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) 
                     firsts[r] = ow == 8 ? *(int64_t *)t0 : *(int32_t *)t0;
                 }
             }
-            DF_NCCL(nccl().GroupStart());
-            for (int r = 0; r < W; r++) {
-                int64_t n = mine[r * rec], nb = mine[r * rec + 1 + 2 * c];
-                if (n) DF_NCCL(nccl().Send(sl[r]->ptr, (size_t)n * 8, ncclChar, r, comm, st));
-                if (nb) DF_NCCL(nccl().Send((const uint8_t *)send[r][c]->values + firsts[r], (size_t)nb, ncclChar, r, comm, st));
-                if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rl->as<int64_t>() + row_off[r], (size_t)cnt(r, me, 0) * 8, ncclChar, r, comm, st));
-                if (cnt(r, me, 1 + 2 * c)) DF_NCCL(nccl().Recv(rd->as<uint8_t>() + byte_off[r], (size_t)cnt(r, me, 1 + 2 * c), ncclChar, r, comm, st));
-            }
-            DF_NCCL(nccl().GroupEnd());
-            for (int r = 0; r < W; r++) if (r != me) ctx->nvlink_bytes += mine[r * rec] * 8 + mine[r * rec + 1 + 2 * c];
-            BufRef starts = make_buf(ctx, (size_t)total * 8 + 16);
-            int64_t tot2 = 0;
-            exclusive_scan_i64(ctx, rl->as<int64_t>(), starts->as<int64_t>(), total, &tot2);
-            int ow = vt.is_large() ? 8 : 4;
-            if (ow == 4 && tbytes > 0x7fffffffLL) fail(DFGPU_EXECUTION, "offset overflow in exchanged Utf8/Binary column");
-            BufRef offs = make_buf(ctx, (size_t)(total + 1) * ow + 16, true);
-            k_offsets_from_starts<<<grid_for(total + 1, 256, ctx, 16), 256, 0, st>>>(starts->as<int64_t>(), total, tbytes, offs->ptr, ow == 8);
-            note_launch(ctx);
-            col->owned.push_back(offs);
-            col->owned.push_back(rd);
-            col->offsets = offs->ptr;
-            col->values = rd->ptr;
-            col->data_bytes = tbytes;
-            keep.insert(keep.end(), sl.begin(), sl.end());
+            const std::vector<ColRef> *sendp = send.data();
+            comm_ops.push_back([=, &mine, &row_off, &cnt]() {
+                for (int r = 0; r < W; r++) {
+                    int64_t n = mine[r * rec], nb = mine[r * rec + 1 + 2 * c];
+                    if (n) DF_NCCL(nccl().Send(sl[r]->ptr, (size_t)n * 8, ncclChar, r, comm, st));
+                    if (nb) DF_NCCL(nccl().Send((const uint8_t *)sendp[r][c]->values + firsts[r], (size_t)nb, ncclChar, r, comm, st));
+                    if (cnt(r, me, 0)) DF_NCCL(nccl().Recv(rl->as<int64_t>() + row_off[r], (size_t)cnt(r, me, 0) * 8, ncclChar, r, comm, st));
+                    if (cnt(r, me, 1 + 2 * c)) DF_NCCL(nccl().Recv(rd->as<uint8_t>() + byte_off[r], (size_t)cnt(r, me, 1 + 2 * c), ncclChar, r, comm, st));
+                    if (r != me) ctx->nvlink_bytes += mine[r * rec] * 8 + mine[r * rec + 1 + 2 * c];
+                }
+            });
+            post_ops.push_back([=]() {
+                BufRef starts = make_buf(ctx, (size_t)total * 8 + 16);
+                int64_t tot2 = 0;
+                exclusive_scan_i64(ctx, rl->as<int64_t>(), starts->as<int64_t>(), total, &tot2);
+                int ow = vt.is_large() ? 8 : 4;
+                if (ow == 4 && tbytes > 0x7fffffffLL) fail(DFGPU_EXECUTION, "offset overflow in exchanged Utf8/Binary column");
+                BufRef offs = make_buf(ctx, (size_t)(total + 1) * ow + 16, true);
+                k_offsets_from_starts<<<grid_for(total + 1, 256, ctx, 16), 256, 0, st>>>(starts->as<int64_t>(), total, tbytes, offs->ptr, ow == 8);
+                note_launch(ctx);
+                col->owned.push_back(offs);
+                col->owned.push_back(rd);
+                col->offsets = offs->ptr;
+                col->values = rd->ptr;
+                col->data_bytes = tbytes;
+            });
         }
         DF_CUDA(cudaGetLastError());
-        ColRef result = col;
-        if (ft.id == T_DICT) result = wrap_trivial_dictionary(ctx, col, ft);
-        out->cols.push_back(result);
-        // send buffers are freed stream-ordered after the collective
     }
+    {
+        KTimer kt(ctx, "stage:exchange_nccl");
+        DF_NCCL(nccl().GroupStart());
+        for (auto &op : comm_ops) op();
+        DF_NCCL(nccl().GroupEnd());
+    }
+    for (auto &op : post_ops) op();
+    DF_CUDA(cudaGetLastError());
+    for (size_t c = 0; c < nc; c++) {
+        ColRef result = cols_out[c];
+        if (schema.fields[c].id == T_DICT) result = wrap_trivial_dictionary(ctx, cols_out[c], schema.fields[c]);
+        out->cols.push_back(result);
+    }
+    // send staging buffers are freed stream-ordered after the collective (the lambdas own them)
     if (total == 0) return nullptr;
     return out.release();
 }

@@ -186,6 +186,14 @@ class DeviceBatch:
         N.check(N.lib().dfgpu_batch_slice(self.ctx.h, self.h, offset, length, C.byref(h)))
         return DeviceBatch(self.ctx, h, keep=self)
 
+    def project(self, columns: Sequence[Union[int, str]]) -> "DeviceBatch":
+        """RecordBatch::project: zero-copy column selection (what ProjectionExec does for plain columns)."""
+        sch = self.schema
+        idx = [_col_index(sch, c) for c in columns]
+        h = C.c_void_p()
+        N.check(N.lib().dfgpu_batch_project(self.ctx.h, self.h, (C.c_int32 * max(1, len(idx)))(*idx), len(idx), C.byref(h)))
+        return DeviceBatch(self.ctx, h, keep=self)
+
     @staticmethod
     def concat(ctx: GpuContext, batches: Sequence["DeviceBatch"]) -> "DeviceBatch":
         arr = (C.c_void_p * len(batches))(*[b.h for b in batches])

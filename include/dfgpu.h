@@ -123,6 +123,10 @@ dfgpu_status dfgpu_batch_concat(dfgpu_ctx *ctx, dfgpu_batch *const *batches, int
 /* zero-copy row slice (RecordBatch::slice; row_hash.rs:478-502 output chunking) */
 dfgpu_status dfgpu_batch_slice(dfgpu_ctx *ctx, const dfgpu_batch *batch, int64_t offset, int64_t length,
                                dfgpu_batch **out);
+/* zero-copy column selection (RecordBatch::project, as ProjectionExec does for plain column
+ * expressions: physical-plan/src/projection.rs); columns share the input's device buffers */
+dfgpu_status dfgpu_batch_project(dfgpu_ctx *ctx, const dfgpu_batch *batch, const int32_t *cols, int32_t n_cols,
+                                 dfgpu_batch **out);
 void dfgpu_batch_free(dfgpu_batch *batch);
 
 /* ---- create_hashes (common/src/hash_utils.rs:357-416) — test hook; seed 0 is the fixed
