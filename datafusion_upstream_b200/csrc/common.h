@@ -175,6 +175,13 @@ struct KTimer {
     }
 };
 
+// communicator wrappers (partition.cu; NCCL is dlopen'd there): byte counts, ctx->stream
+void comm_all_gather(Ctx *ctx, const void *send, void *recv, size_t bytes_per_rank);
+void comm_group_start();
+void comm_group_end();
+void comm_send(Ctx *ctx, const void *p, size_t bytes, int peer);
+void comm_recv(Ctx *ctx, void *p, size_t bytes, int peer);
+
 // device buffer allocated from the stream-ordered pool of ctx->stream
 struct DevBuf {
     Ctx *ctx = nullptr;

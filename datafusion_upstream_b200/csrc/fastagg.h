@@ -59,6 +59,14 @@ struct FaRegPlan {
     int32_t alias[FA_MAX_OPS];    // logical op -> word offset of the accumulator that computes it
 };
 
+// pieces of a partition's records after the record exchange between ranks (level 2 input)
+static const int FA_MAXSEG = 64;
+struct FaSegs {
+    const uint64_t *seg_off = nullptr;  // [nseg][stride] record offsets into the receive buffer
+    const uint32_t *seg_cnt = nullptr;  // [nseg][stride] record counts
+    int nseg = 0, stride = 0;
+};
+
 struct FaOpSpec {
     int kind = 0, nwords = 1;
     int seen_bit = -1;  // ops sharing a NullState share the bit
@@ -90,6 +98,12 @@ class FastAgg {
     void reserve(int64_t rows, int64_t launches);
     // Merge everything pushed so far into dense groups and leave the store empty.
     FaResult finalize();
+    // Collective (every rank of the context's communicator): partition the records pushed so far by
+    // the top hash bits, send every rank the partitions it owns (rank r owns FA_P / world consecutive
+    // partitions) and keep what arrives; finalize() then merges only the owned partitions.  This is
+    // Partial -> RepartitionExec(Hash) -> FinalPartitioned (physical_planner.rs:814-849) fused at the
+    // level of partial-state records: no local final merge, no emit / re-ingest of state batches.
+    void exchange();
     // finalize() + re-insert the groups as partial-state records; returns the exact group count.
     int64_t compact();
     size_t device_bytes() const;
@@ -103,6 +117,10 @@ class FastAgg {
     int S1_ = 0, S2max_ = 0;
     size_t smem1_ = 0, smem2_ = 0;
     BufRef recs_, scalars_, hist_, side_, plan_dev_, regplan_dev_, mode_flag_;
+    // after exchange(): the received records, their pieces per owned partition, and how many there are
+    BufRef xrecs_, xseg_off_, xseg_cnt_;
+    int64_t xR_ = -1;
+    int xfirst_ = 0, xcount_ = 0;  // owned partitions [xfirst_, xfirst_ + xcount_)
     int64_t cap_ = 0, used_ub_ = 0;
     bool reg_mode_allowed_ = true;
     int reg_stages_ = 4;

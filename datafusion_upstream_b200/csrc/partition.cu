@@ -176,6 +176,20 @@ void ctx_destroy_nccl(Ctx *ctx) {
     ctx->nccl_comm = nullptr;
 }
 
+// thin communicator wrappers for the other translation units (fastagg.cu): byte-typed, on ctx->stream
+void comm_all_gather(Ctx *ctx, const void *send, void *recv, size_t bytes_per_rank) {
+    DF_NCCL(nccl().AllGather(send, recv, bytes_per_rank, ncclChar, (ncclComm_t)ctx->nccl_comm, ctx->stream));
+}
+void comm_group_start() { DF_NCCL(nccl().GroupStart()); }
+void comm_group_end() { DF_NCCL(nccl().GroupEnd()); }
+void comm_send(Ctx *ctx, const void *p, size_t bytes, int peer) {
+    DF_NCCL(nccl().Send(p, bytes, ncclChar, peer, (ncclComm_t)ctx->nccl_comm, ctx->stream));
+    if (peer != ctx->opts.rank) ctx->nvlink_bytes += (int64_t)bytes;
+}
+void comm_recv(Ctx *ctx, void *p, size_t bytes, int peer) {
+    DF_NCCL(nccl().Recv(p, bytes, ncclChar, peer, (ncclComm_t)ctx->nccl_comm, ctx->stream));
+}
+
 // ---- exchange helpers --------------------------------------------------------------------------------
 __global__ void k_bitmap_to_bytes(const uint8_t *bm, int64_t bit0, int64_t n, uint8_t *out, int all_one) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
