@@ -280,6 +280,14 @@ def run_ours(args):
             out = op.emit() if to_host else op.emit_device()
             hold[:] = [(op, out)]
             return out
+        if not args.three_op:
+            # fused: level 1 on the local shard -> record exchange (NCCL, one contiguous run per peer) -> level 2 on the owned partitions
+            op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
+            op.push(inp)
+            op.exchange()
+            out = op.emit() if to_host else op.emit_device()
+            hold[:] = [(op, out)]
+            return out
         # Partial -> hash repartition (NCCL all-to-all over NVLink) -> FinalPartitioned
         part = df.GpuAggregateExec(ctx, df.AggregateMode.Partial, w["schema"], w["group_by"], w["exprs"])
         part.push(inp)
@@ -395,7 +403,8 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "int64" if args.workload == "c2" else "i128", "data": "synthetic",
             "config": {"workload": w["name"], "rows_per_gpu": n, "groups": groups, "l2_policy": "inputs larger than L2 (no flush needed)"
                        if w["in_bytes"] > 256e6 else "inputs smaller than L2: table/state reset each step", "mode": "Single" if world == 1 else
-                       f"Partial -> NCCL all-to-all -> FinalPartitioned (dp{world})"},
+                       (f"Partial -> NCCL all-to-all -> FinalPartitioned (dp{world})" if args.three_op else
+                       f"fused Partial -> NCCL record exchange -> FinalPartitioned in one operator per rank (dp{world})")},
             "algorithmic_GBps": algo_bytes * world / (ms_per_step * 1e-3) / 1e9,
             "algorithmic_frac_of_peak": algo_bytes / (ms_per_step * 1e-3) / 1e9 / peak,
             "host_submit_ms": host_ms, "clocks": clk.result, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
@@ -820,6 +829,7 @@ def main():
     ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--three-op", action="store_true", help="N > 1: Partial -> partition -> all-to-all -> FinalPartitioned as three operators instead of the fused record exchange")
     args = ap.parse_args()
     if args.rows <= 0:
         args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000, "q3": 10}[args.workload]   # q3: --rows = scale factor

@@ -15,6 +15,7 @@ const Schema &agg_in_schema(const dfgpu_agg &a);
 Ctx *agg_ctx(const dfgpu_agg &a);
 void agg_metrics(const dfgpu_agg &a, dfgpu_metrics *out);
 int64_t agg_num_groups(dfgpu_agg &a);
+void agg_exchange(dfgpu_agg &a);
 void agg_destroy(dfgpu_agg *a);
 void ctx_init_nccl(Ctx *ctx);
 void ctx_destroy_nccl(Ctx *ctx);
@@ -295,6 +296,12 @@ dfgpu_status dfgpu_agg_num_groups(dfgpu_agg *agg, int64_t *out) {
     DF_TRY
     DF_CUDA(cudaSetDevice(agg_ctx(*agg)->device));
     *out = agg_num_groups(*agg);
+    DF_CATCH
+}
+dfgpu_status dfgpu_agg_exchange(dfgpu_agg *agg) {
+    DF_TRY
+    DF_CUDA(cudaSetDevice(agg_ctx(*agg)->device));
+    agg_exchange(*agg);
     DF_CATCH
 }
 dfgpu_status dfgpu_agg_emit(dfgpu_agg *agg, dfgpu_batch **out) {

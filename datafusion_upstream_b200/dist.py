@@ -57,3 +57,24 @@ def sharded_aggregate(ctx, schema: pa.Schema, group_by: Sequence, aggr_exprs: Se
     if recv is not None:
         fin.push(recv)
     return fin.emit() if to_host else fin.emit_device()
+
+
+def fused_sharded_aggregate(ctx, schema: pa.Schema, group_by: Sequence, aggr_exprs: Sequence, local_batches, world: int, to_host: bool = True):
+    """The same plan fused into one operator per rank (`dfgpu_agg_exchange`): level-1 pre-aggregation of the local
+    shard, partial-state records partitioned by key hash and exchanged over NCCL (one contiguous transfer per peer),
+    final merge of the owned partitions.  Falls back to the three-operator plan when the operator cannot exchange at
+    the record level (the decision depends only on schema and options, so every rank takes the same branch)."""
+    from ._native import DfGpuError
+    from .exec import AggregateMode, GpuAggregateExec
+    op = GpuAggregateExec(ctx, AggregateMode.Single, schema, group_by, aggr_exprs)
+    local_batches = list(local_batches)
+    for b in local_batches:
+        op.push(b)
+    try:
+        op.exchange()
+    except DfGpuError as e:
+        if e.kind != "NotImplemented":
+            raise
+        op.close()
+        return sharded_aggregate(ctx, schema, group_by, aggr_exprs, local_batches, world, to_host)
+    return op.emit() if to_host else op.emit_device()

@@ -292,6 +292,12 @@ class GpuAggregateExec:
             d = DeviceBatch.from_arrow(self.ctx, batch)
             N.check(N.lib().dfgpu_agg_push(self.h, d.h))
 
+    def exchange(self):
+        """Collective: fused Partial -> RepartitionExec(Hash) -> FinalPartitioned (dfgpu_agg_exchange).  After it,
+        emit() returns the finished groups of the keys this rank owns.  Raises DfGpuError(NotImplemented) when the
+        operator cannot exchange at the record level (the caller keeps the three-operator plan)."""
+        N.check(N.lib().dfgpu_agg_exchange(self.h))
+
     def num_groups(self) -> int:
         n = C.c_int64()
         N.check(N.lib().dfgpu_agg_num_groups(self.h, C.byref(n)))

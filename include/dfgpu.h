@@ -155,6 +155,15 @@ dfgpu_status dfgpu_agg_output_schema(const dfgpu_agg *agg, struct ArrowSchema *o
 dfgpu_status dfgpu_agg_push(dfgpu_agg *agg, const dfgpu_batch *batch);
 dfgpu_status dfgpu_agg_push_arrow(dfgpu_agg *agg, const struct ArrowArray *batch);
 dfgpu_status dfgpu_agg_num_groups(dfgpu_agg *agg, int64_t *out);
+/* Sharded aggregation, fused: AggregateExec(Partial) -> RepartitionExec(Hash(group keys), world) ->
+ * AggregateExec(FinalPartitioned) (core/src/physical_planner.rs:814-849) collapsed into ONE operator per
+ * rank.  Collective over the ranks of the context: call it on every rank after the last push and before
+ * emit.  The partial states accumulated so far are partitioned by the group-key hash, every rank receives
+ * the partitions it owns over NCCL (one contiguous transfer per peer), and the following emit returns the
+ * finished groups of the owned keys only - the union over the ranks is the result of the three-operator plan.
+ * world == 1: no-op.  DFGPU_NOT_IMPLEMENTED (before any communication, identically on every rank) when the
+ * operator does not run the two-level path; the caller then keeps the three-operator plan. */
+dfgpu_status dfgpu_agg_exchange(dfgpu_agg *agg);
 /* emit(EmitTo::All) (row_hash.rs:626-662); resets the operator like the reference's
  * early emit (row_hash.rs:723-734) so it can be called mid-stream in Partial mode. */
 dfgpu_status dfgpu_agg_emit(dfgpu_agg *agg, dfgpu_batch **out);

@@ -1,4 +1,6 @@
-"""Two-GPU parity of the sharded path (needs >= 2 GPUs; skipped otherwise): Partial on each rank's row range
+"""Two-GPU parity of the sharded paths (needs >= 2 GPUs; skipped otherwise): the fused operator
+(`dfgpu_agg_exchange`: level-1 records partitioned by key hash, exchanged over NCCL, merged by their owner) and the
+three-operator plan it replaces - Partial on each rank's row range
 -> `dfgpu_partition_hash` -> `dfgpu_exchange_all_to_all` (NCCL) -> FinalPartitioned, against the oracle's Single
 aggregation of the whole table.  Also the join exchange: both sides repartitioned by key owner, per-rank
 Partitioned joins, union equals the oracle's join."""
@@ -52,6 +54,11 @@ def _worker(rank, world, port, n_rows, out_q):
         mine = full.slice(lo, hi - lo)
         exprs = [df.AggregateExpr(df.AggFunc[f.capitalize()], a, nm) for f, a, nm, _ in SPECS]
         out = sharded_aggregate(ctx, full.schema, ["k1", "k2"], exprs, [mine.slice(0, 1000), mine.slice(1000)], world)
+        # the fused operator (dfgpu_agg_exchange): a nullable Int64 key with NULLs and -1 (side groups), a 3-group key
+        # (register mode) and the two-column key above (not a 64-bit image: falls back to the three-operator plan)
+        from datafusion_upstream_b200.dist import fused_sharded_aggregate
+        fused = [fused_sharded_aggregate(ctx, full.schema, gb, exprs, [mine.slice(0, 1000), mine.slice(1000)], world)
+                 for gb in (["k1"], ["k2"], ["k1", "k2"])]
         # join: repartition both sides by key owner, join locally
         left = pa.record_batch([pa.array(np.arange(3000, dtype=np.int64) % 1500), pa.array(np.arange(3000, dtype=np.int32))], names=["a", "x"])
         right = pa.record_batch([pa.array((np.arange(9000, dtype=np.int64) * 7) % 2000), pa.array(np.arange(9000, dtype=np.int32))], names=["b", "y"])
@@ -66,11 +73,14 @@ def _worker(rank, world, port, n_rows, out_q):
         jrows = sum(b.num_rows for b in jout)
         jsum = int(sum(int(np.sum(b.column(1).to_numpy().astype(np.int64) * 31 + b.column(3).to_numpy())) for b in jout))
         import io
-        sink = io.BytesIO()
-        with pa.ipc.new_stream(sink, out.schema) as w:
-            w.write_batch(out)
+
+        def ipc(b):
+            sink = io.BytesIO()
+            with pa.ipc.new_stream(sink, b.schema) as w:
+                w.write_batch(b)
+            return sink.getvalue()
         res = [None] * world
-        dist.all_gather_object(res, (sink.getvalue(), jrows, jsum))
+        dist.all_gather_object(res, (ipc(out), jrows, jsum, [ipc(f) for f in fused]))
         if rank == 0:
             out_q.put(res)
         ctx.synchronize()
@@ -99,11 +109,21 @@ def test_two_gpu_sharded_aggregate_and_join():
         p.join(timeout=120)
         assert p.exitcode == 0
     rows = []
-    for buf, _, _ in res:
+    for buf, _, _, _ in res:
         for b in pa.ipc.open_stream(buf).read_all().to_batches():
             rows += rows_of(b)
     want = oracle_agg("single", [_table(11, n_rows)], ["k1", "k2"], SPECS)
     assert_rows_equal(rows, rows_of(want), key_cols=[0, 1])
+    for i, gb in enumerate((["k1"], ["k2"], ["k1", "k2"])):
+        rows, per_rank = [], []
+        for r in res:
+            got = [x for b in pa.ipc.open_stream(r[3][i]).read_all().to_batches() for x in rows_of(b)]
+            per_rank.append(len(got))
+            rows += got
+        want = oracle_agg("single", [_table(11, n_rows)], gb, SPECS)
+        assert_rows_equal(rows, rows_of(want), key_cols=list(range(len(gb))), what=f"fused {gb}")
+        if gb == ["k1"]:
+            assert min(per_rank) > 0.3 * len(rows) / world   # ownership by hash range: both ranks hold a share
     # join: row count and a checksum over (x, y) equal the oracle's
     left = pa.table({"a": np.arange(3000, dtype=np.int64) % 1500, "x": np.arange(3000, dtype=np.int32)})
     right = pa.table({"b": (np.arange(9000, dtype=np.int64) * 7) % 2000, "y": np.arange(9000, dtype=np.int32)})
