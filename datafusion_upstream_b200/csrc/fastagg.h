@@ -115,7 +115,8 @@ class FastAgg {
     std::vector<FaOpSpec> ops_;
     int SW_ = 0, RW_ = 0, seen_word_ = -1, nbits_ = 0;
     int S1_ = 0, S2max_ = 0;
-    size_t smem1_ = 0, smem2_ = 0;
+    size_t smem1_ = 0, smem2_ = 0, smem2x_ = 0;
+    int S2xmax_ = 0;
     BufRef recs_, scalars_, hist_, side_, plan_dev_, regplan_dev_, mode_flag_;
     // after exchange(): the received records, their pieces per owned partition, and how many there are
     BufRef xrecs_, xseg_off_, xseg_cnt_;
