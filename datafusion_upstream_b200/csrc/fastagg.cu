@@ -203,33 +203,6 @@ DF_D int fa_bucket_find_insert(uint64_t *hkeys, uint32_t b, uint64_t key) {
 DF_D int fa_cache_find_insert(uint64_t *hkeys, int S, uint64_t key, uint64_t h) {
     return fa_bucket_find_insert(hkeys, __umulhi((uint32_t)h, (uint32_t)(S >> 1)), key);
 }
-// Level 2 (must hold every key of the partition): linear probing over buckets.  Returns the slot,
-// or -1 when the key is absent and may not be inserted (occupancy limit reached / probe budget
-// exhausted).  occ is only maintained when the table can fill up (occ_limit != ~0).
-DF_D int fa_find_insert(uint64_t *hkeys, int S, uint64_t key, uint64_t h, int max_probe, uint32_t *occ, uint32_t occ_limit) {
-    const uint32_t nb = (uint32_t)(S >> 1);
-    uint32_t b = __umulhi((uint32_t)h, nb);
-    const bool limited = occ_limit != 0xffffffffu;
-    for (int i = 0; i < max_probe; i++) {
-        ulonglong2 kk = fa_ld_bucket(hkeys + 2 * b);
-        if (kk.x == key) return (int)(2 * b);
-        if (kk.y == key) return (int)(2 * b + 1);
-        if (kk.x == FA_EMPTY || kk.y == FA_EMPTY) {
-            if (limited && *(volatile uint32_t *)occ >= occ_limit) return -1;
-            if (kk.x == FA_EMPTY) {
-                unsigned long long old = atomicCAS((unsigned long long *)&hkeys[2 * b], (unsigned long long)FA_EMPTY, (unsigned long long)key);
-                if (old == FA_EMPTY) { if (limited) atomicAdd(occ, 1u); return (int)(2 * b); }
-                if (old == key) return (int)(2 * b);
-            }
-            unsigned long long old = atomicCAS((unsigned long long *)&hkeys[2 * b + 1], (unsigned long long)FA_EMPTY, (unsigned long long)key);
-            if (old == FA_EMPTY) { if (limited) atomicAdd(occ, 1u); return (int)(2 * b + 1); }
-            if (old == key) return (int)(2 * b + 1);
-        }
-        b = b + 1 == nb ? 0 : b + 1;
-    }
-    return -1;
-}
-
 DF_D void fa_init_table(const FaPlan &pl, uint64_t *hkeys, uint64_t *hstate, int S, int stride, int tid, int nthreads) {
     for (int s = tid; s < stride; s += nthreads) hkeys[s] = FA_EMPTY;
     for (int o = 0; o < pl.nops; o++) {

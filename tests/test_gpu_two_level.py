@@ -91,6 +91,35 @@ def test_side_groups_null_and_all_ones_key(ctx):
     assert_tables_equal(gpu_agg(ctx, "single", [only], ["k"], specs), oracle_agg("single", [only], ["k"], specs), key_cols=[0])
 
 
+@pytest.mark.parametrize("s2max", ["16", "64", "256"])
+def test_overflow_rounds_never_duplicate_a_key(monkeypatch, s2max):
+    """Many rows per key and level-2 tables far smaller than the key set: every partition goes through overflow
+    rounds while thousands of lanes insert the same keys concurrently.  A key must come out of exactly one round
+    (an occupancy-counter criterion once let one lane hand a key to the overflow round while another inserted it:
+    two output rows for one key)."""
+    monkeypatch.setenv("DFGPU_FA_S2MAX", s2max)
+    monkeypatch.setenv("DFGPU_FA_S1", "32")
+    monkeypatch.setenv("DFGPU_FA_SINGLE_MAX", "0")
+    c = gpu_ctx()
+    try:
+        rng = np.random.default_rng(int(s2max))
+        n, card = 600_000, 1500
+        # all keys in few level-2 partitions: sequential small integers hash everywhere, so take keys whose top hash
+        # bits collide rarely but use few distinct keys with ~400 rows each
+        k = pa.array(rng.integers(0, card, n).astype(np.int64) * 7919 - 3, pa.int64())
+        v = pa.array(rng.integers(-50, 50, n), pa.int64())
+        b = pa.record_batch([k, v], names=["k", "v"])
+        specs = [("count", None, "c", None), ("sum", "v", "s", None), ("max", "v", "mx", None)]
+        for _ in range(3):
+            got = gpu_agg(c, "single", [b], ["k"], specs)
+            assert got.num_rows == card
+            assert len(set(got.column(0).to_pylist())) == card
+            assert sum(got.column(1).to_pylist()) == n
+        assert_tables_equal(got, oracle_agg("single", [b], ["k"], specs), key_cols=[0])
+    finally:
+        c.close()
+
+
 def test_register_mode_q1_shape_and_late_keys(ctx):
     """Q1 shape with fixed-width keys (register mode), value nulls, a filter, and keys that first
     appear after the sample the device used to choose the mode (exact per-row slow path)."""
