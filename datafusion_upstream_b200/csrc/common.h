@@ -120,6 +120,16 @@ struct dfgpu_ctx {
     int64_t launches = 0;
     int64_t h2d_bytes = 0, d2h_bytes = 0, nvlink_bytes = 0;
     void *nccl_comm = nullptr;  // ncclComm_t
+    // Receive window of the peer-memory exchange (partition.cu): cudaMalloc'd (IPC-exportable), mapped by every
+    // peer of the communicator; peers[r] = this process' mapping of rank r's window.
+    struct PeerWindow {
+        void *buf = nullptr;
+        size_t bytes = 0;
+        uint64_t gen = 0;
+        int state = 0;  // 0 untried, 1 in use, -1 unavailable on some rank: NCCL send/recv instead
+        struct Peer { uint64_t gen = 0; void *ptr = nullptr; } peers[64];
+        void *scratch = nullptr;  // small device staging for the handle all-gather / barrier
+    } win;
     dfgpu::PinnedPool pinned;
     dfgpu::BufCache bufs;
     uint64_t *flush_dummy = nullptr;
@@ -181,6 +191,14 @@ void comm_group_start();
 void comm_group_end();
 void comm_send(Ctx *ctx, const void *p, size_t bytes, int peer);
 void comm_recv(Ctx *ctx, void *p, size_t bytes, int peer);
+// Peer-memory exchange.  peer_window_prepare is collective: makes this rank's receive window at least `need`
+// bytes, maps every peer's window and returns the mappings in peer_ptrs[world] (own window included); false, on
+// every rank alike, when peer mapping is unavailable.  peer_push copies n runs (src on this device, dst in any
+// mapped window) with one kernel; peer_barrier orders the pushes of all ranks before what follows on the stream.
+bool peer_window_prepare(Ctx *ctx, size_t need, void **peer_ptrs);
+void peer_push(Ctx *ctx, int n, const void *const *src, void *const *dst, const size_t *bytes);
+void peer_barrier(Ctx *ctx);
+void peer_window_destroy(Ctx *ctx);
 
 // device buffer allocated from the stream-ordered pool of ctx->stream
 struct DevBuf {
@@ -199,6 +217,15 @@ struct DevBuf {
 typedef std::shared_ptr<DevBuf> BufRef;
 inline BufRef make_buf(Ctx *c, size_t n, bool zero = false) { return std::make_shared<DevBuf>(c, n, zero); }
 // non-owning window [off, off + n) of another buffer
+// non-owning handle on device memory managed elsewhere (the peer window)
+inline BufRef make_borrowed(Ctx *ctx, void *ptr, size_t n) {
+    BufRef v = std::make_shared<DevBuf>();
+    v->ctx = ctx;
+    v->ptr = ptr;
+    v->bytes = n;
+    v->parent = std::make_shared<DevBuf>();  // (a parent marks the memory as not ours to free)
+    return v;
+}
 inline BufRef make_view(const BufRef &parent, size_t off, size_t n) {
     BufRef v = std::make_shared<DevBuf>();
     v->ctx = parent->ctx;

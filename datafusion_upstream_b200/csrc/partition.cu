@@ -172,6 +172,7 @@ void ctx_init_nccl(Ctx *ctx) {
     ctx->nccl_comm = comm;
 }
 void ctx_destroy_nccl(Ctx *ctx) {
+    peer_window_destroy(ctx);
     if (ctx->nccl_comm) nccl().CommDestroy((ncclComm_t)ctx->nccl_comm);
     ctx->nccl_comm = nullptr;
 }
@@ -188,6 +189,124 @@ void comm_send(Ctx *ctx, const void *p, size_t bytes, int peer) {
 }
 void comm_recv(Ctx *ctx, void *p, size_t bytes, int peer) {
     DF_NCCL(nccl().Recv(p, bytes, ncclChar, peer, (ncclComm_t)ctx->nccl_comm, ctx->stream));
+}
+
+// ---- peer-memory exchange ---------------------------------------------------------------------------
+// NVSwitch gives every GPU full-bandwidth loads / stores into every peer's HBM.  The record exchange of the
+// fused sharded aggregation (fastagg_host.inc) therefore does not go through ncclSend / ncclRecv: every rank
+// exports one receive window (cudaIpcGetMemHandle), maps the windows of its peers once, and a single copy
+// kernel stores each peer's run straight into that peer's window.  NCCL only carries the 80-byte handles and
+// the two barriers.
+struct PushDesc {
+    const void *src[64];
+    void *dst[64];
+    unsigned long long vec[64];  // vectors (16 or 8 bytes) per run
+    int n;
+};
+template <class V>
+__global__ void __launch_bounds__(512) k_peer_push(PushDesc d) {
+    // runs are taken in turn by the whole grid with coalesced vector stores; CTAs start on different peers so all
+    // links are busy at once
+    for (int r = 0; r < d.n; r++) {
+        const int rr = (r + blockIdx.x) % d.n;
+        const V *__restrict__ s = (const V *)d.src[rr];
+        V *__restrict__ t = (V *)d.dst[rr];
+        const unsigned long long nv = d.vec[rr];
+        for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < nv; i += (unsigned long long)gridDim.x * blockDim.x)
+            t[i] = __ldcs(s + i);
+    }
+}
+void peer_push(Ctx *ctx, int n, const void *const *src, void *const *dst, const size_t *bytes) {
+    PushDesc d;
+    memset(&d, 0, sizeof d);
+    bool v16 = true;
+    for (int i = 0; i < n; i++)
+        if (bytes[i]) v16 = v16 && !(bytes[i] & 15) && !((uintptr_t)src[i] & 15) && !((uintptr_t)dst[i] & 15);
+    for (int i = 0; i < n; i++) {
+        if (!bytes[i]) continue;
+        if ((bytes[i] & 7) || ((uintptr_t)src[i] & 7) || ((uintptr_t)dst[i] & 7)) fail(DFGPU_INTERNAL, "peer push: runs must be 8-byte aligned");
+        d.src[d.n] = src[i];
+        d.dst[d.n] = dst[i];
+        d.vec[d.n] = bytes[i] / (v16 ? 16 : 8);
+        d.n++;
+    }
+    if (!d.n) return;
+    if (v16) k_peer_push<uint4><<<ctx->sm_count * 4, 512, 0, ctx->stream>>>(d);
+    else k_peer_push<uint2><<<ctx->sm_count * 4, 512, 0, ctx->stream>>>(d);
+    note_launch(ctx);
+    DF_CUDA(cudaGetLastError());
+}
+void peer_barrier(Ctx *ctx) {
+    auto &w = ctx->win;
+    comm_all_gather(ctx, w.scratch, (uint8_t *)w.scratch + 256, 8);
+}
+void peer_window_destroy(Ctx *ctx) {
+    auto &w = ctx->win;
+    for (auto &p : w.peers) if (p.ptr && p.ptr != w.buf) cudaIpcCloseMemHandle(p.ptr);
+    for (auto &p : w.peers) p = {};
+    if (w.buf) cudaFree(w.buf);
+    if (w.scratch) cudaFree(w.scratch);
+    w.buf = w.scratch = nullptr;
+    w.bytes = 0;
+}
+bool peer_window_prepare(Ctx *ctx, size_t need, void **peer_ptrs) {
+    auto &w = ctx->win;
+    const int W = ctx->opts.world, me = ctx->opts.rank;
+    if (w.state < 0 || W > 64) return false;
+    if (const char *e = getenv("DFGPU_EXCHANGE")) if (!strcmp(e, "nccl")) { w.state = -1; return false; }
+    cudaStream_t st = ctx->stream;
+    struct Msg { cudaIpcMemHandle_t h; uint64_t gen; uint64_t ok; };  // 80 bytes
+    static_assert(sizeof(Msg) == 80, "handle message layout");
+    bool ok = true;
+    if (!w.scratch) ok = cudaMalloc(&w.scratch, 8192) == cudaSuccess && cudaMemset(w.scratch, 0, 8192) == cudaSuccess;  // [0,1024) barrier, [1024,..) handles
+    Msg mine;
+    memset(&mine, 0, sizeof mine);
+    void *retired = nullptr;
+    if (ok && need > w.bytes) {
+        // grow: everything queued on the old window (peers' pushes of the previous exchange were fenced by its barrier)
+        // the old window stays allocated until every peer has dropped its mapping of it (after the second gather)
+        DF_CUDA(cudaStreamSynchronize(st));
+        retired = w.buf;
+        w.buf = nullptr;
+        w.bytes = 0;
+        size_t nb = (need + need / 2 + ((size_t)1 << 20)) & ~(size_t)255;
+        if (cudaMalloc(&w.buf, nb) == cudaSuccess) { w.bytes = nb; w.gen++; }
+        else { cudaGetLastError(); ok = false; }
+    }
+    if (ok && w.buf && cudaIpcGetMemHandle(&mine.h, w.buf) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    mine.gen = w.gen;
+    mine.ok = ok ? 1 : 0;
+    if (!w.scratch) fail(DFGPU_CUDA, "peer window: cannot allocate the staging buffer");
+    uint8_t *stage = (uint8_t *)w.scratch + 1024;             // [Msg mine][Msg all[W]]
+    std::vector<Msg> all((size_t)W);
+    auto gather = [&]() {
+        DF_CUDA(cudaMemcpyAsync(stage, &mine, sizeof mine, cudaMemcpyHostToDevice, st));
+        comm_all_gather(ctx, stage, stage + sizeof(Msg), sizeof(Msg));
+        DF_CUDA(cudaMemcpyAsync(all.data(), stage + sizeof(Msg), sizeof(Msg) * W, cudaMemcpyDeviceToHost, st));
+        DF_CUDA(cudaStreamSynchronize(st));
+    };
+    gather();  // (also the pre-barrier: a peer's window is free once that peer got here)
+    for (int r = 0; r < W; r++) ok = ok && all[(size_t)r].ok;
+    if (ok) {
+        for (int r = 0; r < W && ok; r++) {
+            auto &p = w.peers[r];
+            if (r == me) { p.ptr = w.buf; p.gen = w.gen; continue; }
+            if (p.ptr && p.gen == all[(size_t)r].gen) continue;
+            if (p.ptr) cudaIpcCloseMemHandle(p.ptr);
+            p.ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&p.ptr, all[(size_t)r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); p.ptr = nullptr; ok = false; }
+            p.gen = all[(size_t)r].gen;
+        }
+    }
+    // second round: did every rank manage to map every window?
+    mine.ok = ok ? 1 : 0;
+    gather();
+    for (int r = 0; r < W; r++) ok = ok && all[(size_t)r].ok;
+    if (retired) cudaFree(retired);  // every rank is past its remapping loop
+    if (!ok) { w.state = -1; return false; }
+    w.state = 1;
+    for (int r = 0; r < W; r++) peer_ptrs[r] = w.peers[r].ptr;
+    return true;
 }
 
 // ---- exchange helpers --------------------------------------------------------------------------------
