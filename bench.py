@@ -226,6 +226,21 @@ def build_workload(args, df, ctx, torch, device, rank):
     return w
 
 
+class native_stdout_to_stderr:
+    """NCCL announces its version on the process' stdout (fd 1) when the communicator is created; the contract is ONE
+    JSON line on stdout, so fd 1 points at stderr while the context (and with it the communicator) is set up."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 def pinned_batch(ctx, schema, host_cols, n, torch):
     """Arrow RecordBatch whose buffers live in pinned host memory (PCIe-speed H2D for the e2e leg)."""
     arrays, keep, nbytes = [], [], 0
@@ -257,7 +272,8 @@ def run_ours(args):
         box = [df.GpuContext.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)
         uid = box[0]
-    ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
+    with native_stdout_to_stderr():
+        ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
     w = build_workload(args, df, ctx, torch, device, rank)
     n = args.rows
@@ -454,7 +470,8 @@ def run_join(args):
     device = torch.device("cuda", local)
     from datafusion_upstream_b200.dist import bootstrap_nccl_id, shard_range
     uid = bootstrap_nccl_id(dist, df.GpuContext.nccl_unique_id) if world > 1 else None
-    ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
+    with native_stdout_to_stderr():
+        ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
     B, P = 1_460_000, args.rows
     bt, pt = gen_join(B, P, 42, device, rank, world)
@@ -625,7 +642,8 @@ def run_q3(args):
     device = torch.device("cuda", local)
     from datafusion_upstream_b200.dist import bootstrap_nccl_id
     uid = bootstrap_nccl_id(dist, df.GpuContext.nccl_unique_id) if world > 1 else None
-    ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
+    with native_stdout_to_stderr():
+        ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
     sf = max(1, args.rows)
     ct, ot, lt = gen_q3(sf, 42, device, rank, world)
