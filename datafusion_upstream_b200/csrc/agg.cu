@@ -10,6 +10,7 @@
 //   GLOBAL   one atomic per (row, state word) into HBM-resident state arrays indexed by group id.
 // Both read each input column once, R rows per thread per op so R independent 128-bit loads are
 // in flight per thread.
+#include <functional>
 #include <algorithm>
 #include <cfloat>
 #include <chrono>
@@ -208,7 +209,22 @@ __global__ void k_init_state(uint64_t *state, int nwords, uint64_t lo, uint64_t 
         if (nwords == 2) state[i * nwords + 1] = hi;
     }
 }
-__global__ void k_bytes_to_bitmap(const uint8_t *__restrict__ seen, int64_t G, uint32_t *__restrict__ words) {
+// ---- emit: state -> output columns ---------------------------------------------------------------
+// Every output buffer of an emit is produced by ONE launch: the host records one EmitJob per buffer
+// (values of a state, AVG results, validity bitmaps from seen bytes), uploads the array once, and
+// blockIdx.y picks the job.  (One launch + one allocation per buffer cost ~90 us of host time for
+// the 11 columns of a Q1 result - with 4 output rows.)
+enum { EJ_VALUES = 0, EJ_AVG_F64 = 1, EJ_AVG_DEC128 = 2, EJ_BITMAP = 3 };
+struct EmitJob {
+    int32_t kind, op_kind, out_type, pad;
+    const uint64_t *a;      // state words (values / sums)
+    const uint64_t *b;      // counts (AVG)
+    const uint8_t *seen;    // seen bytes (AVG, bitmap)
+    void *dst;
+    uint64_t factor_lo, factor_hi, lim_lo, lim_hi;  // AVG Decimal128: 10^(s_out - s_in), 10^precision - 1
+    uint32_t *err;
+};
+DF_D void ej_bitmap(const uint8_t *__restrict__ seen, int64_t G, uint32_t *__restrict__ words) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int64_t nround = (G + 31) / 32 * 32;
     for (; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
@@ -218,7 +234,7 @@ __global__ void k_bytes_to_bitmap(const uint8_t *__restrict__ seen, int64_t G, u
     }
 }
 // state words -> output values of type `out_type` (narrowing / un-mapping)
-__global__ void k_emit_values(const uint64_t *__restrict__ state, int kind, int out_type, int64_t G, uint8_t *__restrict__ out) {
+DF_D void ej_values(const uint64_t *__restrict__ state, int kind, int out_type, int64_t G, uint8_t *__restrict__ out) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     for (; i < G; i += (int64_t)gridDim.x * blockDim.x) {
         if (kind == OP_ADD_I128 || kind == OP_MIN_I128 || kind == OP_MAX_I128) {
@@ -241,16 +257,16 @@ __global__ void k_emit_values(const uint64_t *__restrict__ state, int kind, int 
     }
 }
 // AVG evaluate, Float64: sum / count (average.rs:165)
-__global__ void k_avg_f64(const uint64_t *__restrict__ sums, const uint64_t *__restrict__ counts, const uint8_t *__restrict__ seen,
-                          int64_t G, double *__restrict__ out) {
+DF_D void ej_avg_f64(const uint64_t *__restrict__ sums, const uint64_t *__restrict__ counts, const uint8_t *__restrict__ seen, int64_t G,
+                     double *__restrict__ out) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     for (; i < G; i += (int64_t)gridDim.x * blockDim.x)
         out[i] = seen[i] ? __longlong_as_double((long long)sums[i]) / (double)counts[i] : 0.0;
 }
 // AVG evaluate, Decimal128: DecimalAverager::avg (aggregate/utils.rs:108-124) —
 // sum.mul_checked(10^(s_out - s_in)) then truncating division by count, then precision check.
-__global__ void k_avg_dec128(const uint64_t *__restrict__ sums, const uint64_t *__restrict__ counts, const uint8_t *__restrict__ seen,
-                             int64_t G, __int128 factor, __int128 lim, uint64_t *__restrict__ out, uint32_t *__restrict__ err) {
+DF_D void ej_avg_dec128(const uint64_t *__restrict__ sums, const uint64_t *__restrict__ counts, const uint8_t *__restrict__ seen, int64_t G,
+                        __int128 factor, __int128 lim, uint64_t *__restrict__ out, uint32_t *__restrict__ err) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     for (; i < G; i += (int64_t)gridDim.x * blockDim.x) {
         __int128 r = 0;
@@ -271,6 +287,20 @@ __global__ void k_avg_dec128(const uint64_t *__restrict__ sums, const uint64_t *
         }
         out[2 * i] = (uint64_t)(unsigned __int128)r;
         out[2 * i + 1] = (uint64_t)((unsigned __int128)r >> 64);
+    }
+}
+__global__ void __launch_bounds__(256) k_emit_jobs(const EmitJob *__restrict__ jobs, int64_t G) {
+    const EmitJob j = jobs[blockIdx.y];
+    switch (j.kind) {
+    case EJ_VALUES: ej_values(j.a, j.op_kind, j.out_type, G, (uint8_t *)j.dst); break;
+    case EJ_AVG_F64: ej_avg_f64(j.a, j.b, j.seen, G, (double *)j.dst); break;
+    case EJ_AVG_DEC128: {
+        __int128 factor = (__int128)(((unsigned __int128)j.factor_hi << 64) | j.factor_lo);
+        __int128 lim = (__int128)(((unsigned __int128)j.lim_hi << 64) | j.lim_lo);
+        ej_avg_dec128(j.a, j.b, j.seen, G, factor, lim, (uint64_t *)j.dst, j.err);
+        break;
+    }
+    default: ej_bitmap(j.seen, G, (uint32_t *)j.dst); break;
     }
 }
 

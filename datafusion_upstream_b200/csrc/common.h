@@ -2,6 +2,9 @@
 // status/exception bridge, context (device, stream, memory pools, NCCL), device buffers,
 // Arrow type descriptors, device-resident columns and RecordBatches.
 #pragma once
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #include <atomic>
@@ -184,6 +187,16 @@ struct KTimer {
         if (on) cudaEventRecord(ctx->prof[idx].stop, ctx->stream);
     }
 };
+
+// DFGPU_TRACE=1: host-side timeline on stderr (microseconds since the previous trace point, any translation unit)
+inline void df_trace(const char *label) {
+    static const bool on = getenv("DFGPU_TRACE") != nullptr;
+    if (!on) return;
+    static auto last = std::chrono::steady_clock::now();
+    auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[dfgpu trace] %-36s +%8.1f us\n", label, std::chrono::duration<double, std::micro>(now - last).count());
+    last = now;
+}
 
 // communicator wrappers (partition.cu; NCCL is dlopen'd there): byte counts, ctx->stream
 void comm_all_gather(Ctx *ctx, const void *send, void *recv, size_t bytes_per_rank);
