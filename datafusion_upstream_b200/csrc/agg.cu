@@ -64,6 +64,9 @@ __device__ __forceinline__ void combine_raw(int kind, uint64_t &lo, uint64_t &hi
     case OP_MAX_F64: if (__longlong_as_double((long long)lo) < __longlong_as_double((long long)blo)) lo = blo; break;
     case OP_MIN_I128: if (lt128_signed(u128_t{blo, bhi}, u128_t{lo, hi})) { lo = blo; hi = bhi; } break;
     case OP_MAX_I128: if (lt128_signed(u128_t{lo, hi}, u128_t{blo, bhi})) { lo = blo; hi = bhi; } break;
+    case OP_AND_U64: lo &= blo; break;
+    case OP_OR_U64: lo |= blo; break;
+    case OP_XOR_U64: lo ^= blo; break;
     }
 }
 
@@ -79,6 +82,9 @@ __device__ __forceinline__ void apply_global(const OpDesc &op, uint32_t g, uint6
     case OP_MAX_U64: atomicMax((unsigned long long *)st, (unsigned long long)lo); break;
     case OP_MIN_F64: { double d = __longlong_as_double((long long)lo); if (d == d) atomicMin((unsigned long long *)st, (unsigned long long)f64_to_ordered(d)); break; }
     case OP_MAX_F64: { double d = __longlong_as_double((long long)lo); if (d == d) atomicMax((unsigned long long *)st, (unsigned long long)f64_to_ordered(d)); break; }
+    case OP_AND_U64: atomicAnd((unsigned long long *)st, (unsigned long long)lo); break;
+    case OP_OR_U64: atomicOr((unsigned long long *)st, (unsigned long long)lo); break;
+    case OP_XOR_U64: atomicXor((unsigned long long *)st, (unsigned long long)lo); break;
     case OP_MIN_I128: case OP_MAX_I128: {
         u128_t v{lo, hi};
         u128_t cur{0, 0};
@@ -214,7 +220,7 @@ __global__ void k_init_state(uint64_t *state, int nwords, uint64_t lo, uint64_t 
 // (values of a state, AVG results, validity bitmaps from seen bytes), uploads the array once, and
 // blockIdx.y picks the job.  (One launch + one allocation per buffer cost ~90 us of host time for
 // the 11 columns of a Q1 result - with 4 output rows.)
-enum { EJ_VALUES = 0, EJ_AVG_F64 = 1, EJ_AVG_DEC128 = 2, EJ_BITMAP = 3 };
+enum { EJ_VALUES = 0, EJ_AVG_F64 = 1, EJ_AVG_DEC128 = 2, EJ_BITMAP = 3, EJ_BOOL_VALUES = 4 };
 struct EmitJob {
     int32_t kind, op_kind, out_type, pad;
     const uint64_t *a;      // state words (values / sums)
@@ -229,6 +235,16 @@ DF_D void ej_bitmap(const uint8_t *__restrict__ seen, int64_t G, uint32_t *__res
     int64_t nround = (G + 31) / 32 * 32;
     for (; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
         bool v = i < G && seen[i] != 0;
+        uint32_t m = __ballot_sync(0xffffffffu, v);
+        if ((threadIdx.x & 31) == 0) words[i >> 5] = m;
+    }
+}
+// state words of a Boolean accumulator (0 / 1) -> bit-packed Boolean values (bool_op.rs:105-121)
+DF_D void ej_bool_values(const uint64_t *__restrict__ state, int64_t G, uint32_t *__restrict__ words) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int64_t nround = (G + 31) / 32 * 32;
+    for (; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+        bool v = i < G && state[i] != 0;
         uint32_t m = __ballot_sync(0xffffffffu, v);
         if ((threadIdx.x & 31) == 0) words[i >> 5] = m;
     }
@@ -300,6 +316,7 @@ __global__ void __launch_bounds__(256) k_emit_jobs(const EmitJob *__restrict__ j
         ej_avg_dec128(j.a, j.b, j.seen, G, factor, lim, (uint64_t *)j.dst, j.err);
         break;
     }
+    case EJ_BOOL_VALUES: ej_bool_values(j.a, G, (uint32_t *)j.dst); break;
     default: ej_bitmap(j.seen, G, (uint32_t *)j.dst); break;
     }
 }

@@ -85,7 +85,7 @@ struct FaResult {
 class FastAgg {
   public:
     FastAgg(Ctx *ctx, const std::vector<FaOpSpec> &ops);
-    static bool kind_supported(int kind) { return kind != OP_MIN_I128 && kind != OP_MAX_I128; }
+    static bool kind_supported(int kind) { return kind != OP_MIN_I128 && kind != OP_MAX_I128 && kind < OP_AND_U64; }
     int SW() const { return SW_; }
     int seen_word() const { return seen_word_; }
     const std::vector<FaOpSpec> &ops() const { return ops_; }

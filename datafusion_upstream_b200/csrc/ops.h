@@ -13,7 +13,8 @@ enum OpKind : int32_t {
     OP_ADD_I128 = 5,   // wrapping 128-bit integer sum (Decimal128)
     OP_MIN_I64 = 6, OP_MAX_I64 = 7, OP_MIN_U64 = 8, OP_MAX_U64 = 9,
     OP_MIN_F64 = 10, OP_MAX_F64 = 11,  // strict compares, NaN never replaces (min_max.rs:102-139)
-    OP_MIN_I128 = 12, OP_MAX_I128 = 13
+    OP_MIN_I128 = 12, OP_MAX_I128 = 13,
+    OP_AND_U64 = 14, OP_OR_U64 = 15, OP_XOR_U64 = 16  // BIT_AND/OR/XOR, BOOL_AND/OR (bit_and_or_xor.rs:123-126, bool_op.rs:92-101)
 };
 
 struct OpDesc {

@@ -34,6 +34,11 @@ class AggFunc(IntEnum):
     Avg = 3
     Min = 4
     Max = 5
+    BitAnd = 6      # bit_and_or_xor.rs (integer arguments)
+    BitOr = 7
+    BitXor = 8
+    BoolAnd = 9     # bool_and_or.rs (Boolean argument, BooleanGroupsAccumulator)
+    BoolOr = 10
 
 
 class JoinType(IntEnum):

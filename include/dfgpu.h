@@ -47,7 +47,11 @@ enum {
     DFGPU_AGG_SINGLE_PARTITIONED = 4
 };
 /* the GroupsAccumulator implementations on the path */
-enum { DFGPU_SUM = 1, DFGPU_COUNT = 2, DFGPU_AVG = 3, DFGPU_MIN = 4, DFGPU_MAX = 5 };
+enum { DFGPU_SUM = 1, DFGPU_COUNT = 2, DFGPU_AVG = 3, DFGPU_MIN = 4, DFGPU_MAX = 5,
+       /* the remaining GroupsAccumulator implementations of the reference —
+        * physical-expr/src/aggregate/bit_and_or_xor.rs:116-140, 281-301, 442-462 (integer types) and
+        * bool_and_or.rs:137-148, 270-281 (Boolean; BooleanGroupsAccumulator, groups_accumulator/bool_op.rs) */
+       DFGPU_BIT_AND = 6, DFGPU_BIT_OR = 7, DFGPU_BIT_XOR = 8, DFGPU_BOOL_AND = 9, DFGPU_BOOL_OR = 10 };
 /* JoinType — common/src/join_type.rs:30-47 */
 enum {
     DFGPU_JOIN_INNER = 0, DFGPU_JOIN_LEFT = 1, DFGPU_JOIN_RIGHT = 2, DFGPU_JOIN_FULL = 3,

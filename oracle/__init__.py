@@ -30,7 +30,8 @@ _LIB_PATH = os.path.join(_HERE, "liboracle.so")
  OT_DATE64, OT_TS, OT_TIME32, OT_TIME64, OT_DEC128, OT_UTF8, OT_LARGE_UTF8, OT_BINARY,
  OT_LARGE_BINARY, OT_DICT) = range(1, 23)
 
-AGG_FUNCS = {"sum": 1, "count": 2, "avg": 3, "min": 4, "max": 5}
+AGG_FUNCS = {"sum": 1, "count": 2, "avg": 3, "min": 4, "max": 5,
+             "bit_and": 6, "bit_or": 7, "bit_xor": 8, "bool_and": 9, "bool_or": 10}
 MODES = {"partial": 0, "final": 1, "final_partitioned": 2, "single": 3, "single_partitioned": 4}
 JOIN_TYPES = {"inner": 0, "left": 1, "right": 2, "full": 3, "left_semi": 4, "right_semi": 5,
               "left_anti": 6, "right_anti": 7}
@@ -303,6 +304,8 @@ def state_fields(a: AggSpec):
     if a.func == "avg": return [(f"{a.name}[count]", pa.uint64()), (f"{a.name}[sum]", avg_sum_type(a.input_type))]
     if a.func == "min": return [(f"{a.name}[min]", _value_type(a.input_type))]
     if a.func == "max": return [(f"{a.name}[max]", _value_type(a.input_type))]
+    if a.func in ("bit_and", "bit_or", "bit_xor", "bool_and", "bool_or"):   # bit_and_or_xor.rs:96-102, bool_and_or.rs:117-123
+        return [(f"{a.name}[{a.func}]", _value_type(a.input_type))]
     raise OracleError(a.func)
 
 

@@ -714,6 +714,75 @@ template <bool IS_MIN> static Acc *make_minmax(const oagg_desc &d) {
     return nullptr;
 }
 
+// BIT_AND / BIT_OR / BIT_XOR — PrimitiveGroupsAccumulator over the argument's own integer type with
+// starting value !0 (AND) or 0 (OR, XOR) (aggregate/bit_and_or_xor.rs:116-140, 281-301, 442-462;
+// groups_accumulator/prim_op.rs:86-139).  State == evaluate; merge == update.
+template <class T, int OP> struct BitAcc : Acc {
+    std::vector<T> vals;
+    std::vector<uint8_t> seen;
+    int type = 0;
+    void update(const uint32_t *g, int64_t n, const ocol *const *args, const ocol *filt, size_t ng) override {
+        vals.resize(ng, OP == 0 ? (T)~(T)0 : (T)0); seen.resize(ng, 0);
+        accumulate(g, n, args[0], filt, &seen, [&](uint32_t gi, const ocol *vc, int64_t vi) {
+            T v;
+            memcpy(&v, (const uint8_t *)vc->values + sizeof(T) * vi, sizeof(T));
+            if (OP == 0) vals[gi] &= v; else if (OP == 1) vals[gi] |= v; else vals[gi] ^= v;
+        });
+    }
+    void merge(const uint32_t *g, int64_t n, const ocol *const *args, size_t ng) override { update(g, n, args, nullptr, ng); }
+    bool evaluate(int64_t first_n, OutCol &o) override {
+        auto v = take_needed(vals, first_n);
+        auto s = take_needed(seen, first_n);
+        o.type = type;
+        put_values(o, v);
+        o.set_validity(s);
+        return true;
+    }
+    bool state(int64_t first_n, std::vector<OutCol> &out) override {
+        out.emplace_back();
+        return evaluate(first_n, out.back());
+    }
+};
+template <int OP> static Acc *make_bit(const oagg_desc &d) {
+#define BB(TT, CT) case TT: { auto *a = new BitAcc<CT, OP>(); a->type = d.input_type; return a; }
+    switch (d.input_type) {
+        BB(OT_I8, int8_t) BB(OT_I16, int16_t) BB(OT_I32, int32_t) BB(OT_I64, int64_t)
+        BB(OT_U8, uint8_t) BB(OT_U16, uint16_t) BB(OT_U32, uint32_t) BB(OT_U64, uint64_t)
+    }
+#undef BB
+    return nullptr;  // downcast_integer! accepts the eight integer types only
+}
+
+// BOOL_AND / BOOL_OR — BooleanGroupsAccumulator (groups_accumulator/bool_op.rs:38-140,
+// bool_and_or.rs:137-148, 270-281).  The value bit of a NEW group starts at bool::default() = false
+// for both functions (bool_op.rs:82-85), so the grouped BOOL_AND of this reference version yields
+// false for every group that saw a value (false && x); that is reproduced, not corrected.
+template <bool IS_AND> struct BoolAcc : Acc {
+    std::vector<uint8_t> vals, seen;
+    void update(const uint32_t *g, int64_t n, const ocol *const *args, const ocol *filt, size_t ng) override {
+        vals.resize(ng, 0); seen.resize(ng, 0);
+        accumulate(g, n, args[0], filt, &seen, [&](uint32_t gi, const ocol *vc, int64_t vi) {
+            bool nv = bits64(vc, vi) != 0, cur = vals[gi] != 0;
+            vals[gi] = IS_AND ? (cur && nv) : (cur || nv);
+        });
+    }
+    void merge(const uint32_t *g, int64_t n, const ocol *const *args, size_t ng) override { update(g, n, args, nullptr, ng); }
+    bool evaluate(int64_t first_n, OutCol &o) override {
+        auto v = take_needed(vals, first_n);
+        auto s = take_needed(seen, first_n);
+        o.type = OT_BOOL;
+        o.values.assign((v.size() + 7) / 8, 0);
+        for (size_t i = 0; i < v.size(); i++)
+            if (v[i]) set_bit(o.values.data(), (int64_t)i);
+        o.set_validity(s);
+        return true;
+    }
+    bool state(int64_t first_n, std::vector<OutCol> &out) override {
+        out.emplace_back();
+        return evaluate(first_n, out.back());
+    }
+};
+
 static Acc *make_acc(const oagg_desc &d) {
     int t = d.input_type;
     switch (d.func) {
@@ -740,6 +809,11 @@ static Acc *make_acc(const oagg_desc &d) {
         return nullptr;
     case OAGG_MIN: return make_minmax<true>(d);
     case OAGG_MAX: return make_minmax<false>(d);
+    case OAGG_BIT_AND: return make_bit<0>(d);
+    case OAGG_BIT_OR: return make_bit<1>(d);
+    case OAGG_BIT_XOR: return make_bit<2>(d);
+    case OAGG_BOOL_AND: return t == OT_BOOL ? new BoolAcc<true>() : nullptr;
+    case OAGG_BOOL_OR: return t == OT_BOOL ? new BoolAcc<false>() : nullptr;
     }
     return nullptr;
 }

@@ -229,6 +229,47 @@ def agg_cases():
     d["count_by_c1_c4"], d["count_by_c1_c4_src"] = after(
         "select count(*),c1,c4 from decimal_simple group by c1,c4 order by c1,c4;")
     out["decimal_slt"] = d
+    # aggregate.slt: grouped BIT_AND / BIT_OR / BIT_XOR over `bit_aggregate_functions`
+    # (the table literal and the `GROUP BY tag` answer; SMALLINT columns, c3 nullable)
+    aslt = read("datafusion/sqllogictest/test_files/aggregate.slt")
+    i = next(k for k, l in enumerate(aslt) if l.startswith("create table bit_aggregate_functions"))
+    j = next(k for k in range(i, len(aslt)) if aslt[k].strip() == "as values")
+    rows = []
+    k = j + 1
+    while aslt[k].strip().startswith("("):
+        vals = [v.strip() for v in aslt[k].strip().rstrip(",;").strip("()").split(",")]
+        rows.append([None if v == "null" else (v.strip("'") if v.startswith("'") else int(v)) for v in vals])
+        k += 1
+    q = next(m for m in range(k, len(aslt)) if aslt[m].strip() == "GROUP BY tag")
+    r = next(m for m in range(q, len(aslt)) if aslt[m].strip() == "----") + 1
+    ans = []
+    while aslt[r].strip():
+        t = aslt[r].split()
+        ans.append([None if v == "NULL" else int(v) for v in t[:-1]] + [t[-1]])
+        r += 1
+    out["bit_aggregate_slt"] = {
+        "source": "datafusion/sqllogictest/test_files/aggregate.slt:%d-%d" % (i + 1, r),
+        "columns": ["c1", "c2", "c3", "tag"], "rows": rows,
+        "result_columns": ["bit_and(c1)", "bit_and(c2)", "bit_and(c3)", "bit_or(c1)", "bit_or(c2)", "bit_or(c3)",
+                           "bit_xor(c1)", "bit_xor(c2)", "bit_xor(c3)", "tag"],
+        "expected": ans}
+    # bit_and_or_xor.rs unit tests: generic_test_op!(array, type, Op, expected scalar)
+    bsrc = read("datafusion/physical-expr/src/aggregate/bit_and_or_xor.rs")
+    units = []
+    for n, l in enumerate(bsrc):
+        m = re.match(r"\s*fn (bit_(and|or|xor)_[iu]32\w*)\(\)", l)
+        if not m or "distinct" in m.group(1):
+            continue
+        body = " ".join(x.strip() for x in bsrc[n + 1:n + 12])
+        body = body[:body.index("generic_test_op!") + body[body.index("generic_test_op!"):].index(")") + 40]
+        vec = re.search(r"vec!\[(.*?)\]\)\)", body).group(1)
+        items = [None if t.strip() == "None" else int(re.sub(r"[^0-9-]", "", t.replace("_u32", "").replace("Some", "")))
+                 for t in vec.split(",") if t.strip()]
+        exp = re.search(r"ScalarValue::(?:from\((\d+)[iu]32\)|Int32\(None\))", body)
+        units.append({"name": m.group(1), "op": "bit_" + m.group(2), "unsigned": "_u32" in m.group(1),
+                      "input": items, "expected": None if exp.group(1) is None else int(exp.group(1)),
+                      "source": "datafusion/physical-expr/src/aggregate/bit_and_or_xor.rs:%d" % (n + 1)})
+    out["bit_unit_tests"] = units
     return out
 
 

@@ -6,7 +6,7 @@ import pyarrow as pa
 import oracle
 from oracle import AggSpec, OracleAgg
 
-FUNCS = {"sum": 1, "count": 2, "avg": 3, "min": 4, "max": 5}
+FUNCS = {"sum": 1, "count": 2, "avg": 3, "min": 4, "max": 5, "bit_and": 6, "bit_or": 7, "bit_xor": 8, "bool_and": 9, "bool_or": 10}
 
 
 def gpu_ctx(**kw):

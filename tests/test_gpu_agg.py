@@ -251,3 +251,69 @@ def test_not_implemented_and_plan_errors(ctx):
     with pytest.raises(df.DfGpuError) as e:
         gpu_agg(ctx, "single", [b], [7], [("count", None, "c", None)])
     assert e.value.kind == "Plan"
+
+
+# ---- BIT_AND / BIT_OR / BIT_XOR (bit_and_or_xor.rs) and BOOL_AND / BOOL_OR (bool_and_or.rs) ----
+BIT_SPECS = [
+    ("bit_and", "i", "BIT_AND(i)", None), ("bit_or", "i", "BIT_OR(i)", None), ("bit_xor", "i", "BIT_XOR(i)", None),
+    ("bit_and", "s", "BIT_AND(s)", None), ("bit_or", "u", "BIT_OR(u)", None), ("bit_xor", "b8", "BIT_XOR(b8)", None),
+    ("bit_and", "u", "BIT_AND(u) FILTER", "flt"), ("bit_xor", "s", "BIT_XOR(s) FILTER", "flt"),
+    ("bool_and", "flt", "BOOL_AND(flt)", None), ("bool_or", "flt", "BOOL_OR(flt)", None), ("count", None, "COUNT(*)", None),
+    ("sum", "i", "SUM(i)", None),
+]
+
+
+def test_golden_bit_aggregate_slt(ctx):
+    """aggregate.slt:1768-1813: grouped bit_and / bit_or / bit_xor over SMALLINT columns, `GROUP BY tag`."""
+    g = AGGS["bit_aggregate_slt"]
+    cols = list(zip(*g["rows"]))
+    b = pa.record_batch([pa.array(list(cols[0]), pa.int16()), pa.array(list(cols[1]), pa.int16()), pa.array(list(cols[2]), pa.int16()),
+                         pa.array(list(cols[3]), pa.string())], names=g["columns"])
+    specs = [(f, n, f"{f}({n})", None) for f in ("bit_and", "bit_or", "bit_xor") for n in ("c1", "c2", "c3")]
+    want = [tuple([r[-1]] + r[:-1]) for r in g["expected"]]
+    out = gpu_agg(ctx, "single", [b], ["tag"], specs)
+    assert [f.type for f in out.schema][1:] == [pa.int16()] * 9
+    assert_rows_equal(rows_of(out), want)
+    st = [gpu_agg(ctx, "partial", [b.slice(0, 2)], ["tag"], specs), gpu_agg(ctx, "partial", [b.slice(2)], ["tag"], specs)]
+    assert st[0].schema.names[1] == "bit_and(c1)[bit_and]" and st[0].schema.names[9] == "bit_xor(c3)[bit_xor]"
+    out = gpu_agg(ctx, "final", st, [0], [(f, None, n, None) for f, _, n, _ in specs])
+    assert_rows_equal(rows_of(out), want)
+
+
+@pytest.mark.parametrize("case", AGGS["bit_unit_tests"], ids=[c["name"] for c in AGGS["bit_unit_tests"]])
+def test_golden_bit_unit_vectors(ctx, case):
+    t = pa.uint32() if case["unsigned"] else pa.int32()      # bit_and_or_xor.rs:708-787
+    v = pa.array(case["input"], t)
+    b = pa.record_batch([pa.array([0] * len(v), pa.int8()), v], names=["k", "v"])
+    out = gpu_agg(ctx, "single", [b], ["k"], [(case["op"], "v", "r", None)])
+    assert out.schema.field(1).type == t
+    assert out.column(1).to_pylist() == [case["expected"]]
+
+
+@pytest.mark.parametrize("keys,card", [(["int64"], 37), (["utf8", "int32"], 37), (["int64"], 5000), (["dict_utf8"], 400)],
+                         ids=["int64-private", "utf8+int32", "int64-global", "dict"])
+@pytest.mark.parametrize("nulls", [False, True], ids=["nonull", "nulls"])
+def test_bit_bool_ops_vs_oracle(ctx, keys, card, nulls):
+    rng = np.random.default_rng(77 + card + nulls)
+    batches = [make_table(rng, n, keys, card, 0.1 if nulls else 0.0, 0.2 if nulls else 0.0) for n in (3000, 1, 0, 9001)]
+    gk = [f"k{i}" for i in range(len(keys))]
+    got = gpu_agg(ctx, "single", batches, gk, BIT_SPECS)
+    want = oracle_agg("single", batches, gk, BIT_SPECS)
+    assert_tables_equal(got, want, key_cols=list(range(len(keys))), what="bit/bool single " + str(keys))
+    # Partial per partition -> FinalPartitioned
+    parts = [batches[:1], batches[1:]]
+    g_states = [gpu_agg(ctx, "partial", p, gk, BIT_SPECS) for p in parts]
+    o_states = [oracle_agg("partial", p, gk, BIT_SPECS) for p in parts]
+    for gs, os_ in zip(g_states, o_states):
+        assert_tables_equal(gs, os_, key_cols=list(range(len(keys))), what="bit/bool partial state")
+    fs = [(f, None, n, None) for f, _, n, _ in BIT_SPECS]
+    got = gpu_agg(ctx, "final_partitioned", g_states, list(range(len(keys))), fs)
+    assert_rows_equal(rows_of(got), rows_of(want), key_cols=list(range(len(keys))))
+
+
+def test_bit_ops_reject_unsupported_types(ctx):
+    b = pa.record_batch([pa.array([1, 2], pa.int32()), pa.array([1.0, 2.0]), pa.array([1, 2], pa.int32())], names=["k", "f", "i"])
+    with pytest.raises(Exception, match="not implemented|NotImplemented"):
+        gpu_agg(ctx, "single", [b], ["k"], [("bit_and", "f", "x", None)])       # downcast_integer! -> not_impl_err
+    with pytest.raises(Exception, match="not implemented|NotImplemented"):
+        gpu_agg(ctx, "single", [b], ["k"], [("bool_or", "i", "x", None)])       # bool_and_or.rs:142-146

@@ -176,3 +176,58 @@ def test_emit_first_n_and_float_minmax_quirks():
     # min_max.rs:102-139: NaN never replaces the start value; start values are finite f64::MIN/MAX
     assert rows_of(first) == [(1, -sys.float_info.max, sys.float_info.max, 2), (2, -sys.float_info.max, float("-inf"), 1)]
     assert rows_of(rest) == [(3, 1.5, 1.5, 1), (4, None, None, 0)]
+
+
+def _bit_slt_inputs():
+    g = AGGS["bit_aggregate_slt"]
+    cols = list(zip(*g["rows"]))
+    c = {n: pa.array(list(v), pa.int16()) for n, v in zip(g["columns"][:3], cols[:3])}   # SMALLINT
+    tag = pa.array(list(cols[3]), pa.string())
+    specs = [(f, n) for f in ("bit_and", "bit_or", "bit_xor") for n in ("c1", "c2", "c3")]
+    want = [tuple([r[-1]] + r[:-1]) for r in g["expected"]]
+    return c, tag, specs, want
+
+
+def test_bit_aggregate_slt():
+    # aggregate.slt:1795-1813 — grouped BIT_AND / BIT_OR / BIT_XOR, NULL for a group without values
+    c, tag, specs, want = _bit_slt_inputs()
+    a = OracleAgg("single", ["tag"], [pa.string()], [AggSpec(f, f"{f}({n})", pa.int16()) for f, n in specs])
+    a.push([tag], [c[n] for _, n in specs])
+    out = a.emit()
+    assert [f.type for f in out.schema][1:] == [pa.int16()] * 9
+    assert_rows_equal(rows_of(out), want)
+    # Partial (state == value, names `x[bit_and]`, bit_and_or_xor.rs:96-102) -> Final
+    p = OracleAgg("partial", ["tag"], [pa.string()], [AggSpec(f, f"{f}({n})", pa.int16()) for f, n in specs])
+    p.push([tag.slice(0, 2)], [c[n].slice(0, 2) for _, n in specs])
+    s1 = p.emit()
+    p.push([tag.slice(2)], [c[n].slice(2) for _, n in specs])
+    s2 = p.emit()
+    assert s1.schema.names[1] == "bit_and(c1)[bit_and]" and s1.schema.names[9] == "bit_xor(c3)[bit_xor]"
+    f = OracleAgg("final", ["tag"], [pa.string()], [AggSpec(fn, f"{fn}({n})", pa.int16()) for fn, n in specs])
+    for s in (s1, s2):
+        f.push([s.column(0)], [s.column(i) for i in range(1, 10)])
+    assert_rows_equal(rows_of(f.emit()), want)
+
+
+@pytest.mark.parametrize("case", AGGS["bit_unit_tests"], ids=[c["name"] for c in AGGS["bit_unit_tests"]])
+def test_bit_unit_vectors(case):
+    # bit_and_or_xor.rs:708-787 (generic_test_op! known answers)
+    t = pa.uint32() if case["unsigned"] else pa.int32()
+    v = pa.array(case["input"], t)
+    a = OracleAgg("single", ["k"], [pa.int8()], [AggSpec(case["op"], "r", t)])
+    a.push([pa.array([0] * len(v), pa.int8())], [v])
+    out = a.emit()
+    assert out.schema.field(1).type == t
+    assert out.column(1).to_pylist() == [case["expected"]]
+
+
+def test_bool_and_or_groups_accumulator():
+    # BooleanGroupsAccumulator (bool_op.rs:76-103): a new group's value bit starts at false for BOTH functions,
+    # so grouped BOOL_AND is false whenever the group saw a value; NULL when it saw none.
+    k = pa.array([1, 1, 2, 2, 3, 4, 4], pa.int32())
+    v = pa.array([True, True, False, True, None, False, False], pa.bool_())
+    a = OracleAgg("single", ["k"], [pa.int32()], [AggSpec("bool_and", "a", pa.bool_()), AggSpec("bool_or", "o", pa.bool_())])
+    a.push([k], [v, v])
+    out = a.emit()
+    assert out.schema.field(1).type == pa.bool_()
+    assert_rows_equal(rows_of(out), [(1, False, True), (2, False, True), (3, None, None), (4, False, False)])
