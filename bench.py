@@ -71,6 +71,46 @@ def gen_c2_keys(n, seed, device, universe=85_000_000):
     return out
 
 
+def gen_c5(n, seed, device, phrases=6_000_000, regions=9_000):
+    """ClickBench-shaped (RegionID Int32, SearchPhrase Utf8) key columns (SURVEY §8d C5): RegionID Zipf over ~9 K ids;
+    SearchPhrase empty for 70 % of the rows, otherwise Zipf over ~6 M distinct phrases whose lengths are geometric in
+    1..80 bytes (mean ~20).  Returns (region i32[n], offsets i32[n+1], data u8[total])."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    # phrase table: phrase p (p >= 1) is `len_p` bytes derived from a counter-based mixer, so equal ids give equal bytes
+    plen = torch.empty(phrases + 1, dtype=torch.int64, device=device)
+    u = torch.rand(phrases + 1, generator=g, device=device, dtype=torch.float64)
+    plen[:] = torch.clamp((torch.log1p(-u) / math.log(1 - 1 / 20.0)).to(torch.int64) + 1, 1, 80)
+    plen[0] = 0                                              # id 0 = the empty phrase
+    region = torch.empty(n, dtype=torch.int32, device=device)
+    pid = torch.empty(n, dtype=torch.int64, device=device)
+    step = 1 << 24
+    for o in range(0, n, step):
+        m = min(step, n - o)
+        u = torch.rand(m, generator=g, device=device, dtype=torch.float64)
+        region[o:o + m] = (torch.exp(u * math.log(regions)).to(torch.int64) * 7 + 1).to(torch.int32)
+        u = torch.rand(m, generator=g, device=device, dtype=torch.float64)
+        e = torch.rand(m, generator=g, device=device) < 0.7
+        r = torch.exp(u * math.log(phrases)).to(torch.int64).clamp_(1, phrases)
+        pid[o:o + m] = torch.where(e, torch.zeros_like(r), r)
+    lens = plen[pid]
+    offsets = torch.zeros(n + 1, dtype=torch.int64, device=device)
+    torch.cumsum(lens, 0, out=offsets[1:])
+    total = int(offsets[-1])
+    assert total < 2**31 - 1, "SearchPhrase bytes exceed i32 offsets; lower --rows"
+    data = torch.empty(total, dtype=torch.uint8, device=device)
+    bstep = 1 << 27
+    for o in range(0, total, bstep):                          # bytes [o, o + m): which row, which byte of its phrase
+        m = min(bstep, total - o)
+        pos = torch.arange(o, o + m, device=device, dtype=torch.int64)
+        row = torch.searchsorted(offsets, pos, right=True) - 1
+        k = pos - offsets[row]
+        h = _mix64_torch(pid[row] * 128 + k)
+        data[o:o + m] = (97 + (h & 0xF)).to(torch.uint8)     # 'a'..'p'
+    return region, offsets.to(torch.int32), data
+
+
 def gen_q1(n, seed, device):
     """lineitem-shaped columns: 2 key columns with the TPC-H joint distribution, 5 Decimal128 columns."""
     import torch
@@ -220,6 +260,37 @@ def build_workload(args, df, ctx, torch, device, rank):
             d = [cols[c][:sample].cpu().numpy() for c in ("qty", "price", "disc_price", "charge", "disc")]
             return oracle.bench_q1(f, s, d, threads)
         w["cpu"] = cpu
+    elif args.workload == "c5":
+        region, offsets, data = gen_c5(n, 42 + rank, device)
+        schema = pa.schema([("RegionID", pa.int32()), ("SearchPhrase", pa.string())])
+        w["name"] = (f"ClickBench-shaped GROUP BY RegionID, SearchPhrase COUNT(*), {n} rows, Int32 x Utf8 keys (70% empty phrase, Zipf over "
+                     f"6M phrases of 1-80 bytes, {int(data.numel())} string bytes) - variable-width GroupValues interning (BASELINE configs[4])")
+        w["dev"] = df.DeviceBatch.from_device(ctx, schema, [{"buffers": [None, region.data_ptr()], "null_count": 0},
+                                                            {"buffers": [None, offsets.data_ptr(), data.data_ptr()], "null_count": 0}],
+                                              n, keep=(region, offsets, data))
+        w["schema"] = schema
+        w["group_by"] = ["RegionID", "SearchPhrase"]
+        w["exprs"] = [df.AggregateExpr(df.AggFunc.Count, None, "COUNT(*)")]
+        w["in_bytes"] = 4 * n + 4 * (n + 1) + int(data.numel())
+        w["out_row_bytes"] = 4 + 4 + 8          # RegionID + phrase offset + count (the distinct phrases' own bytes are not counted)
+        host_cols = [("RegionID", pa.int32(), region), ("SearchPhrase", pa.string(), (offsets, data))]
+
+        def cpu(threads, sample):
+            # the oracle's generic operator (GroupValuesRows, row.rs:94-146), single-threaded, 8192-row batches
+            import time as _t
+            hb = pa.record_batch([pa.array(region[:sample].cpu().numpy()),
+                                  pa.Array.from_buffers(pa.string(), sample, [None, pa.py_buffer(offsets[:sample + 1].cpu().numpy()),
+                                                                             pa.py_buffer(data.cpu().numpy())])], schema=schema)
+            o = oracle.OracleAgg("single", ["RegionID", "SearchPhrase"], [pa.int32(), pa.string()], [oracle.AggSpec("count", "COUNT(*)", None)])
+            t0 = _t.perf_counter()
+            for off in range(0, sample, 8192):
+                s = hb.slice(off, 8192)
+                o.push([s.column(0), s.column(1)], [None])
+            out = o.emit()
+            return _t.perf_counter() - t0, out.num_rows, 0
+        w["cpu"] = cpu
+        w["cpu_threads"] = 1
+        w["cpu_sample"] = 4_000_000
     else:
         raise SystemExit(f"unknown workload {args.workload}")
     w["host_cols"] = host_cols
@@ -245,13 +316,15 @@ def pinned_batch(ctx, schema, host_cols, n, torch):
     """Arrow RecordBatch whose buffers live in pinned host memory (PCIe-speed H2D for the e2e leg)."""
     arrays, keep, nbytes = [], [], 0
     for name, typ, t in host_cols:
-        src = t.contiguous().cpu().numpy().reshape(-1).view(np.uint8)
-        ptr = ctx.host_alloc(src.nbytes)
-        ctypes.memmove(ptr, src.ctypes.data, src.nbytes)
-        buf = pa.foreign_buffer(ptr, src.nbytes)
-        arrays.append(pa.Array.from_buffers(typ, n, [None, buf]))
-        keep.append(ptr)
-        nbytes += src.nbytes
+        bufs = [None]
+        for part in (t if isinstance(t, tuple) else (t,)):      # var-width columns: (offsets, data)
+            src = part.contiguous().cpu().numpy().reshape(-1).view(np.uint8)
+            ptr = ctx.host_alloc(max(src.nbytes, 1))
+            ctypes.memmove(ptr, src.ctypes.data, src.nbytes)
+            bufs.append(pa.foreign_buffer(ptr, src.nbytes))
+            keep.append(ptr)
+            nbytes += src.nbytes
+        arrays.append(pa.Array.from_buffers(typ, n, bufs))
     return pa.RecordBatch.from_arrays(arrays, schema=schema), keep, nbytes
 
 
@@ -273,7 +346,7 @@ def run_ours(args):
         dist.broadcast_object_list(box, src=0)
         uid = box[0]
     with native_stdout_to_stderr():
-        ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid)
+        ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid, coalesce_rows=args.coalesce_rows)
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
     w = build_workload(args, df, ctx, torch, device, rank)
     n = args.rows
@@ -361,6 +434,24 @@ def run_ours(args):
     if not args.no_e2e:
         hb, keep, h2d = pinned_batch(ctx, w["schema"], w["host_cols"], n, torch)
         e2e_steps = max(1, min(args.steps, 5))
+        exported = []
+        if args.batch_rows > 0 and world == 1:
+            # the reference's batch granularity (8192 rows, common/src/config.rs:215): one dfgpu_agg_push_arrow per slice of
+            # the pinned host batch; the C-Data structs are exported before the timed region (a Rust caller has them for free)
+            from datafusion_upstream_b200 import _native as N
+            for o in range(0, n, args.batch_rows):
+                a, sc = N.ArrowArray(), N.ArrowSchema()
+                hb.slice(o, args.batch_rows)._export_to_c(ctypes.addressof(a), ctypes.addressof(sc))
+                exported.append((a, sc))
+            L = N.lib()
+
+            def step(inp, to_host=True):  # noqa: F811 - e2e leg only
+                op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
+                for a, _ in exported:
+                    N.check(L.dfgpu_agg_push_arrow(op.h, ctypes.addressof(a)))
+                out = op.emit()
+                hold[:] = [(op, out)]
+                return out
         step(hb, to_host=True)
         hold.clear()
         barrier()
@@ -381,6 +472,13 @@ def run_ours(args):
             dist.all_reduce(t)
             dt, h2d, d2h = float(tmax[0]), int(t[1]), int(t[2])
         e2e = {"value": n * world / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3}
+        if exported:
+            e2e["batch_rows"] = args.batch_rows
+            e2e["pushes_per_step"] = len(exported)
+            for a, sc in exported:
+                if a.release:
+                    ctypes.CFUNCTYPE(None, ctypes.POINTER(N.ArrowArray))(a.release)(ctypes.byref(a))
+                N.release_schema(sc)
         del hb
         for p in keep:
             ctx.host_free(p)
@@ -407,16 +505,17 @@ def run_ours(args):
     # ---- CPU baseline (the oracle port, reference-shaped parallel plan) on rank 0 ----
     cpu = None
     if rank == 0 and not args.no_cpu:
-        threads = os.cpu_count() or 1
-        sample = min(n, args.cpu_sample)
+        threads = w.get("cpu_threads") or os.cpu_count() or 1
+        sample = min(n, w.get("cpu_sample") or args.cpu_sample)
         secs, g, _ = w["cpu"](threads, sample)
+        shape = "P=%d Partial -> hash repartition -> FinalPartitioned" % threads if threads > 1 else "one Single-mode operator (scalar port)"
         cpu = {"value": sample / secs, "unit": "rows/s", "cores": threads, "kind": "port",
-               "sample": f"first {sample} rows of the same workload, P={threads} Partial -> hash repartition -> FinalPartitioned, 8192-row batches"}
+               "sample": f"first {sample} rows of the same workload, {shape}, 8192-row batches"}
     if rank == 0:
         line = {
             "metric": "input rows/s (hash aggregation, device-resident input) and HBM GB/s", "value": value, "unit": "rows/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "int64" if args.workload == "c2" else "i128", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": {"c2": "int64", "c5": "u8"}.get(args.workload, "i128"), "data": "synthetic",
             "config": {"workload": w["name"], "rows_per_gpu": n, "groups": groups, "l2_policy": "inputs larger than L2 (no flush needed)"
                        if w["in_bytes"] > 256e6 else "inputs smaller than L2: table/state reset each step", "mode": "Single" if world == 1 else
                        (f"Partial -> NCCL all-to-all -> FinalPartitioned (dp{world})" if args.three_op else
@@ -841,18 +940,22 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--workload", default="c2", choices=["c2", "q1", "join", "q3"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "q1", "join", "q3", "c5"])
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=50_000_000)
     ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--batch-rows", type=int, default=0, help="e2e leg: push the host batch in slices of this many rows (8192 = the reference's batch_size)")
+    ap.add_argument("--coalesce-rows", type=int, default=0, help="dfgpu_options.coalesce_rows (0 = default 1 Mi, -1 = off)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--three-op", action="store_true", help="N > 1: Partial -> partition -> all-to-all -> FinalPartitioned as three operators instead of the fused record exchange")
     args = ap.parse_args()
     if args.rows <= 0:
-        args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000, "q3": 10}[args.workload]   # q3: --rows = scale factor
+        args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000, "q3": 10, "c5": 100_000_000}[args.workload]   # q3: --rows = scale factor
     if args.warmup < 3 and args.impl != "reference":
         args.warmup = max(args.warmup, 3)       # timing rules: W >= 3
+    if args.workload == "c5":
+        args.three_op = True     # string keys: the fused record exchange covers 64-bit key images only
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "join":

@@ -50,7 +50,7 @@ class Options(C.Structure):
     _fields_ = [
         ("device", C.c_int32), ("batch_size", C.c_int32), ("memory_limit", C.c_int64), ("load_factor", C.c_double),
         ("force_hash_collisions", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-        ("nccl_unique_id", C.c_void_p), ("chunk_rows", C.c_int64),
+        ("nccl_unique_id", C.c_void_p), ("chunk_rows", C.c_int64), ("coalesce_rows", C.c_int64),
     ]
 
 

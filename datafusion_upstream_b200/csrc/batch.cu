@@ -2,6 +2,7 @@
 // (take / concat / slice / bitmap realign / prefix sum) that stand in for arrow-rs
 // `compute::{take, concat_batches}` on the device (joins/utils.rs:1180-1230, hash_join.rs:764).
 #include <algorithm>
+#include <array>
 
 #include "common.h"
 #include "device.cuh"
@@ -1210,3 +1211,5 @@ Batch *batch_concat(Ctx *ctx, Batch *const *batches, int n) {
 }
 
 }  // namespace dfgpu
+
+#include "coalesce.inc"

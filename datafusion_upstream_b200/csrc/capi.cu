@@ -9,6 +9,8 @@ struct dfgpu_agg;
 namespace dfgpu {
 dfgpu_agg *agg_create(Ctx *ctx, int mode, const Schema &in, const int32_t *group_cols, int n_group, const dfgpu_agg_desc *descs, int n_aggs);
 void agg_push(dfgpu_agg &a, const Batch &batch);
+void agg_push_host(dfgpu_agg &a, const ArrowArray *batch);
+void agg_flush_pending(dfgpu_agg &a);
 Batch *agg_emit(dfgpu_agg &a);
 const Schema &agg_out_schema(const dfgpu_agg &a);
 const Schema &agg_in_schema(const dfgpu_agg &a);
@@ -281,6 +283,7 @@ dfgpu_status dfgpu_agg_output_schema(const dfgpu_agg *agg, ArrowSchema *out) {
 dfgpu_status dfgpu_agg_push(dfgpu_agg *agg, const dfgpu_batch *batch) {
     DF_TRY
     DF_CUDA(cudaSetDevice(agg_ctx(*agg)->device));
+    agg_flush_pending(*agg);
     agg_push(*agg, *batch);
     DF_CATCH
 }
@@ -288,8 +291,7 @@ dfgpu_status dfgpu_agg_push_arrow(dfgpu_agg *agg, const ArrowArray *batch) {
     DF_TRY
     Ctx *ctx = agg_ctx(*agg);
     DF_CUDA(cudaSetDevice(ctx->device));
-    std::unique_ptr<Batch> b(batch_import(ctx, batch, agg_in_schema(*agg), false));
-    agg_push(*agg, *b);
+    agg_push_host(*agg, batch);
     DF_CATCH
 }
 dfgpu_status dfgpu_agg_num_groups(dfgpu_agg *agg, int64_t *out) {

@@ -300,6 +300,30 @@ typedef dfgpu_batch Batch;
 Batch *batch_import(Ctx *ctx, const ArrowArray *arr, const Schema &schema, bool on_device);
 void batch_export(Ctx *ctx, const Batch *b, ArrowArray *out, ArrowSchema *out_schema);
 Batch *batch_concat(Ctx *ctx, Batch *const *batches, int n);
+// Host-side CoalesceBatches (coalesce.inc): packs small host Arrow batches into a pinned arena, one H2D per buffer per flush.
+class HostCoalescer {
+  public:
+    HostCoalescer(Ctx *ctx, const Schema &schema, int64_t target_rows);
+    ~HostCoalescer();
+    HostCoalescer(const HostCoalescer &) = delete;
+    HostCoalescer &operator=(const HostCoalescer &) = delete;
+    static bool supports(const Schema &schema);   // fixed-width, Boolean and Utf8/Binary columns; no dictionaries
+    int64_t rows() const { return rows_; }
+    int64_t target() const { return target_; }
+    int64_t flushes() const { return flushes_; }
+    bool fits(const ArrowArray *batch) const;     // false: flush first (i32 offsets of a Utf8 column would overflow)
+    void append(const ArrowArray *batch);         // copies; the caller may release the batch afterwards
+    Batch *flush();                               // nullptr when empty
+  private:
+    struct Col;
+    Ctx *ctx_;
+    Schema schema_;
+    int64_t target_, rows_ = 0, flushes_ = 0;
+    Col *sets_[2] = {nullptr, nullptr};
+    cudaEvent_t ev_[2] = {nullptr, nullptr};
+    bool pending_[2] = {false, false};
+    int cur_ = 0;
+};
 Batch *batch_slice(Ctx *ctx, const Batch *b, int64_t off, int64_t len);
 // gather rows (compute::take); idx < 0 => NULL row.  idx is a device array of n int64.
 ColRef col_take(Ctx *ctx, const DevCol &src, const int64_t *idx, int64_t n, bool idx_may_be_null);

@@ -62,12 +62,13 @@ class GpuContext:
 
     def __init__(self, device: int = 0, batch_size: int = 8192, memory_limit: int = 0, load_factor: float = 0.5,
                  force_hash_collisions: bool = False, rank: int = 0, world: int = 1, nccl_unique_id: Optional[bytes] = None,
-                 chunk_rows: int = 0):
+                 chunk_rows: int = 0, coalesce_rows: int = 0):
         L = N.lib()
         o = N.Options()
         L.dfgpu_options_default(C.byref(o))
         o.device, o.batch_size, o.memory_limit, o.load_factor = device, batch_size, memory_limit, load_factor
         o.force_hash_collisions, o.rank, o.world, o.chunk_rows = int(force_hash_collisions), rank, world, chunk_rows
+        o.coalesce_rows = coalesce_rows
         self._uid = None
         if nccl_unique_id is not None:
             self._uid = C.create_string_buffer(nccl_unique_id, 128)
@@ -294,8 +295,18 @@ class GpuAggregateExec:
         if isinstance(batch, DeviceBatch):
             N.check(N.lib().dfgpu_agg_push(self.h, batch.h))
         else:
-            d = DeviceBatch.from_arrow(self.ctx, batch)
-            N.check(N.lib().dfgpu_agg_push(self.h, d.h))
+            # host Arrow batch: the call the Rust shim makes (dfgpu_agg_push_arrow); small batches are packed into a
+            # pinned arena by the library and cross PCIe as one (dfgpu_options.coalesce_rows)
+            if batch.schema.types != self.input_schema.types:
+                raise N.DfGpuError(1, f"Internal error: pushed batch schema {batch.schema.types} != operator input schema {self.input_schema.types}")
+            a, s = N.ArrowArray(), N.ArrowSchema()
+            batch._export_to_c(C.addressof(a), C.addressof(s))
+            try:
+                N.check(N.lib().dfgpu_agg_push_arrow(self.h, C.addressof(a)))
+            finally:
+                if a.release:
+                    C.CFUNCTYPE(None, C.POINTER(N.ArrowArray))(a.release)(C.byref(a))
+                N.release_schema(s)
 
     def exchange(self):
         """Collective: fused Partial -> RepartitionExec(Hash) -> FinalPartitioned (dfgpu_agg_exchange).  After it,

@@ -77,6 +77,10 @@ typedef struct dfgpu_options {
     int32_t rank, world;           /* this process' GPU rank / number of GPUs (1 = no NCCL)    */
     const void *nccl_unique_id;    /* 128-byte ncclUniqueId shared by all ranks, or NULL       */
     int64_t chunk_rows;            /* rows per internal launch wave, 0 = default (4 Mi)         */
+    int64_t coalesce_rows;         /* dfgpu_agg_push_arrow packs host batches smaller than half of this into a pinned
+                                      arena and pushes them as one (CoalesceBatchesExec, physical-plan/src/
+                                      coalesce_batches.rs, moved to the PCIe boundary); 0 = default (1 Mi rows),
+                                      < 0 = off.  Ignored under a memory_limit (per-batch accounting)          */
 } dfgpu_options;
 
 typedef struct dfgpu_metrics {     /* BaselineMetrics + BuildProbeJoinMetrics

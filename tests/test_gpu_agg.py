@@ -317,3 +317,43 @@ def test_bit_ops_reject_unsupported_types(ctx):
         gpu_agg(ctx, "single", [b], ["k"], [("bit_and", "f", "x", None)])       # downcast_integer! -> not_impl_err
     with pytest.raises(Exception, match="not implemented|NotImplemented"):
         gpu_agg(ctx, "single", [b], ["k"], [("bool_or", "i", "x", None)])       # bool_and_or.rs:142-146
+
+
+@pytest.mark.parametrize("keys", [["utf8", "int32"], ["int64"], ["large_utf8"], ["bool", "int16"]], ids=lambda k: "+".join(k))
+@pytest.mark.parametrize("target", [3000, 64, -1], ids=["coalesce3000", "coalesce64", "off"])
+def test_host_batch_coalescing(keys, target):
+    """dfgpu_agg_push_arrow packs small host batches into a pinned arena (CoalesceBatchesExec at the PCIe boundary,
+    dfgpu_options.coalesce_rows): slices with arbitrary offsets (validity / Boolean bit offsets, Utf8 offset rebasing),
+    flushes in the middle of the stream, batches large enough to bypass the arena, empty batches."""
+    ctx = gpu_ctx(coalesce_rows=target)
+    rng = np.random.default_rng(len(keys) * 1000 + target + 5)
+    whole = make_table(rng, 20_000, keys, 211, 0.1, 0.2)
+    lens = [1, 7, 0, 500, 1499, 13, 1501, 64, 8, 8, 3, 2900, 29, 6000, 1, 1, 300]
+    pieces, off = [], 0
+    while off < whole.num_rows:
+        for ln in lens:
+            ln = min(ln, whole.num_rows - off)
+            pieces.append(whole.slice(off, ln))
+            off += ln
+            if off >= whole.num_rows:
+                break
+    specs = SPECS + BIT_SPECS[:10]
+    gk = [f"k{i}" for i in range(len(keys))]
+    got = gpu_agg(ctx, "single", pieces, gk, specs)
+    want = oracle_agg("single", [whole], gk, specs)
+    assert_tables_equal(got, want, key_cols=list(range(len(keys))), what=f"coalescing {keys} target={target}")
+    # num_groups() in the middle of the stream sees the rows still waiting in the arena
+    import datafusion_upstream_b200 as df
+    op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, whole.schema, gk, [df.AggregateExpr(df.AggFunc.Count, None, "c")])
+    for p in pieces[:9]:
+        op.push(p)
+    seen = sum(p.num_rows for p in pieces[:9])
+    ref = oracle_agg("single", [whole.slice(0, seen)], gk, [("count", None, "c", None)])
+    assert op.num_groups() == ref.num_rows
+    for p in pieces[9:]:
+        op.push(p)
+    out = op.emit()
+    assert sum(out.column(len(keys)).to_pylist()) == whole.num_rows
+    assert op.metrics()["input_batches"] == len(pieces) and op.metrics()["input_rows"] == whole.num_rows
+    op.close()
+    ctx.close()
