@@ -138,6 +138,21 @@ __global__ void __launch_bounds__(ACC_T) k_accumulate(const OpDesc *__restrict__
                 lo[k] = 1; hi[k] = 0;
             }
             const int cat = op_category(op.kind);
+            if (!PRIVATE && op.kind == OP_COUNT) {
+                // COUNT: warp-level pre-aggregation before the global atomic — the lanes of a warp that hit the same
+                // group elect one lane, which adds their number (hot keys: one atomic per warp instead of one per row)
+#pragma unroll
+                for (int k = 0; k < ACC_R; k++) {
+                    const unsigned m = __ballot_sync(0xffffffffu, acc[k]);
+                    if (!acc[k]) continue;
+                    const unsigned peers = __match_any_sync(m, g[k]);
+                    if ((tid & 31) == __ffs(peers) - 1) {
+                        atomicAdd((unsigned long long *)(op.state + g[k]), (unsigned long long)__popc(peers));
+                        if (op.seen) op.seen[g[k]] = 1;
+                    }
+                }
+                continue;
+            }
             if (cat == 1) {
 #pragma unroll
                 for (int k = 0; k < ACC_R; k++)

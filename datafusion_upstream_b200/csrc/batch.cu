@@ -1212,4 +1212,109 @@ Batch *batch_concat(Ctx *ctx, Batch *const *batches, int n) {
 
 }  // namespace dfgpu
 
+
+// ------------------------------------------------------------------------------------------------
+// FilterExec: batch_filter -> arrow `filter_record_batch` (physical-plan/src/filter.rs:315-327): keep the rows whose
+// predicate value is true and not NULL, in input order.  Two passes over the predicate BITMAP (1 bit per row): block
+// counts, a scan of the (n / 4096) block counts, then every block writes the row numbers of its survivors at its
+// offset (warp ballots give the rank inside the block, so the order is the input order).  The survivors' columns are
+// then gathered with the take kernels.
+// ------------------------------------------------------------------------------------------------
+namespace dfgpu {
+static const int FLT_T = 256, FLT_R = 16;  // rows of one block = FLT_T * FLT_R
+DF_D bool pred_true(const ColView &m, int64_t i) { return col_valid(m, i) && bit_get((const uint8_t *)m.values, m.dbit + i); }
+
+__global__ void __launch_bounds__(FLT_T) k_filter_count(ColView m, int64_t n, int64_t *__restrict__ block_counts) {
+    const int64_t base = (int64_t)blockIdx.x * FLT_T * FLT_R;
+    int c = 0;
+#pragma unroll 4
+    for (int k = 0; k < FLT_R; k++) {
+        int64_t row = base + (int64_t)k * FLT_T + threadIdx.x;
+        c += (row < n && pred_true(m, row)) ? 1 : 0;
+    }
+    __shared__ int wsum[FLT_T / 32];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < FLT_T / 32; w++) t += wsum[w];
+        block_counts[blockIdx.x] = t;
+    }
+}
+__global__ void __launch_bounds__(FLT_T) k_filter_indices(ColView m, int64_t n, const int64_t *__restrict__ block_offs, int64_t *__restrict__ idx) {
+    const int64_t base = (int64_t)blockIdx.x * FLT_T * FLT_R;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ int wcnt[FLT_R][FLT_T / 32];
+    bool keep[FLT_R];
+    unsigned bal[FLT_R];
+#pragma unroll
+    for (int k = 0; k < FLT_R; k++) {
+        int64_t row = base + (int64_t)k * FLT_T + threadIdx.x;
+        keep[k] = row < n && pred_true(m, row);
+        bal[k] = __ballot_sync(0xffffffffu, keep[k]);
+        if (lane == 0) wcnt[k][warp] = __popc(bal[k]);
+    }
+    __syncthreads();
+    // rank of (k, warp) = survivors of all earlier (k', warp') in row order: k major, warp minor
+    int64_t out = block_offs[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < FLT_R; k++) {
+        int before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < FLT_T / 32; w++) {
+            int c = wcnt[k][w];
+            before += w < warp ? c : 0;
+            total += c;
+        }
+        if (keep[k]) idx[out + before + __popc(bal[k] & ((1u << lane) - 1))] = base + (int64_t)k * FLT_T + threadIdx.x;
+        out += total;
+    }
+}
+
+Batch *batch_filter(Ctx *ctx, const Batch *b, int predicate_col) {
+    if (predicate_col < 0 || predicate_col >= (int)b->cols.size()) fail(DFGPU_PLAN, "filter: predicate column index out of range");
+    const DevCol &p = *b->cols[(size_t)predicate_col];
+    if (p.type.id != T_BOOL) fail(DFGPU_PLAN, "filter: predicate column must be Boolean");  // as_boolean_array (filter.rs:323)
+    const int64_t n = b->num_rows;
+    cudaStream_t st = ctx->stream;
+    std::unique_ptr<Batch> out(new Batch());
+    out->ctx = ctx;
+    int64_t total = 0;
+    BufRef idx;
+    if (n > 0) {
+        const int64_t nblk = (n + FLT_T * FLT_R - 1) / (FLT_T * FLT_R);
+        BufRef counts = make_buf(ctx, (size_t)nblk * 8 + 16), offs = make_buf(ctx, (size_t)nblk * 8 + 16);
+        {
+            KTimer kt(ctx, "k_filter_count", n / 8);
+            k_filter_count<<<(unsigned)nblk, FLT_T, 0, st>>>(p.view(), n, counts->as<int64_t>());
+        }
+        exclusive_scan_i64(ctx, counts->as<int64_t>(), offs->as<int64_t>(), nblk, &total);
+        idx = make_buf(ctx, (size_t)total * 8 + 16);
+        if (total) {
+            KTimer kt(ctx, "k_filter_indices", n / 8 + total * 8);
+            k_filter_indices<<<(unsigned)nblk, FLT_T, 0, st>>>(p.view(), n, offs->as<int64_t>(), idx->as<int64_t>());
+        }
+        note_launch(ctx, 2);
+        DF_CUDA(cudaGetLastError());
+    } else {
+        idx = make_buf(ctx, 16);
+    }
+    out->num_rows = total;
+    std::vector<const DevCol *> srcs;
+    std::vector<const int64_t *> idxs;
+    std::vector<bool> maybe_null;
+    for (auto &c : b->cols) {
+        srcs.push_back(c.get());
+        idxs.push_back(idx->as<int64_t>());
+        maybe_null.push_back(false);
+    }
+    KTimer kt(ctx, "stage:filter_take");
+    out->cols = cols_take(ctx, srcs, idxs, total, maybe_null);
+    for (size_t i = 0; i < out->cols.size(); i++) out->cols[i]->type = b->cols[i]->type;
+    return out.release();
+}
+}  // namespace dfgpu
+
 #include "coalesce.inc"

@@ -243,6 +243,13 @@ dfgpu_status dfgpu_batch_project(dfgpu_ctx *ctx, const dfgpu_batch *b, const int
     *out = o.release();
     DF_CATCH
 }
+dfgpu_status dfgpu_batch_filter(dfgpu_ctx *ctx, const dfgpu_batch *b, int32_t predicate_col, dfgpu_batch **out) {
+    DF_TRY
+    if (!b || !out) fail(DFGPU_INTERNAL, "null argument");
+    DF_CUDA(cudaSetDevice(ctx->device));
+    *out = batch_filter(ctx, b, predicate_col);
+    DF_CATCH
+}
 void dfgpu_batch_free(dfgpu_batch *b) {
     if (!b) return;
     cudaSetDevice(b->ctx->device);

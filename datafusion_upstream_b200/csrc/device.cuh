@@ -36,21 +36,32 @@ DF_HD uint64_t h_u128(uint64_t lo, uint64_t hi, uint64_t seed) {
 // combine_hashes (hash_utils.rs:38-41)
 DF_HD uint64_t combine_hashes(uint64_t l, uint64_t r) { return (17ULL * 37ULL + l) * 37ULL + r; }
 
-DF_D uint64_t load_le(const uint8_t *p, int n) {  // n in 1..8, unaligned
-    uint64_t w = 0;
-    for (int i = 0; i < n; i++) w |= (uint64_t)p[i] << (8 * i);
-    return w;
+// n bytes (1..8) at an arbitrary address as a little-endian word, read with one or two ALIGNED 64-bit loads
+// (Utf8 values start at any byte; a byte loop costs eight loads per word).  An aligned word that holds at least one
+// byte of the range lies in the same page as that byte, so neither load can fault; bytes outside the range are
+// shifted or masked away.  CG: read through L2 (data another SM may have just published).
+template <bool CG = false> DF_D uint64_t load_le(const uint8_t *p, int n) {
+    const uintptr_t a = (uintptr_t)p;
+    const uint64_t *w = (const uint64_t *)(a & ~(uintptr_t)7);
+    const int o = (int)(a & 7), sh = o * 8;
+    uint64_t v = (CG ? __ldcg(w) : *w) >> sh;
+    if (o + n > 8) v |= (CG ? __ldcg(w + 1) : w[1]) << (64 - sh);  // o >= 1 here
+    if (n < 8) v &= (1ULL << (8 * n)) - 1;
+    return v;
 }
 DF_D uint64_t h_bytes(const uint8_t *p, int64_t len, uint64_t seed) {
     uint64_t h = h_u64((uint64_t)len, seed);
     int64_t i = 0;
-    if ((((uintptr_t)p) & 7) == 0) {
-        for (; i + 8 <= len; i += 8) h = mix64(h ^ *(const uint64_t *)(p + i));
-    } else {
-        for (; i + 8 <= len; i += 8) h = mix64(h ^ load_le(p + i, 8));
-    }
+    for (; i + 8 <= len; i += 8) h = mix64(h ^ load_le(p + i, 8));
     if (i < len) h = mix64(h ^ load_le(p + i, (int)(len - i)));
     return h;
+}
+// a[0, len) == b[0, len), eight bytes per step; CG: b is read through L2
+template <bool CG = false> DF_D bool bytes_equal(const uint8_t *a, const uint8_t *b, int64_t len) {
+    int64_t k = 0;
+    for (; k + 8 <= len; k += 8)
+        if (load_le(a + k, 8) != load_le<CG>(b + k, 8)) return false;
+    return k == len || load_le(a + k, (int)(len - k)) == load_le<CG>(b + k, (int)(len - k));
 }
 
 // ---- column access ----------------------------------------------------------------------------

@@ -123,11 +123,6 @@ __device__ __forceinline__ uint64_t hash_row_words(const uint8_t *p, int W) {
     for (int k = 0; k < W; k += 8) h = mix64(h ^ *(const uint64_t *)(p + k));
     return h;
 }
-__device__ __forceinline__ bool bytes_equal(const uint8_t *a, const uint8_t *b, int64_t len) {
-    for (int64_t k = 0; k < len; k++)
-        if (a[k] != b[k]) return false;
-    return true;
-}
 __device__ __forceinline__ bool words_equal(const uint8_t *a, const uint8_t *b, int W) {
     for (int k = 0; k < W; k += 8)
         if (*(const uint64_t *)(a + k) != *(const uint64_t *)(b + k)) return false;
@@ -199,10 +194,7 @@ __global__ void __launch_bounds__(256) k_intern_rows(TableView t, const uint8_t 
                 } else if (VAR) {
                     // the key store is written by other SMs during this kernel: bypass the (non-coherent) L1
                     eq = __ldcg(&t.glen[pl]) == (int32_t)klen;
-                    if (eq) {
-                        const uint8_t *sp = t.heap + __ldcg(&t.goff[pl]);
-                        for (int64_t k = 0; k < klen && eq; k++) eq = __ldcg(sp + k) == kp[k];
-                    }
+                    if (eq) eq = bytes_equal<true>(kp, t.heap + __ldcg(&t.goff[pl]), klen);
                 } else {
                     const uint8_t *sp = t.grows + (uint64_t)pl * W;
                     eq = true;

@@ -200,6 +200,12 @@ class DeviceBatch:
         N.check(N.lib().dfgpu_batch_project(self.ctx.h, self.h, (C.c_int32 * max(1, len(idx)))(*idx), len(idx), C.byref(h)))
         return DeviceBatch(self.ctx, h, keep=self)
 
+    def filter(self, predicate: Union[int, str]) -> "DeviceBatch":
+        """FilterExec::batch_filter (filter.rs:315-327): rows where the Boolean column `predicate` is true and not NULL."""
+        h = C.c_void_p()
+        N.check(N.lib().dfgpu_batch_filter(self.ctx.h, self.h, _col_index(self.schema, predicate), C.byref(h)))
+        return DeviceBatch(self.ctx, h)
+
     @staticmethod
     def concat(ctx: GpuContext, batches: Sequence["DeviceBatch"]) -> "DeviceBatch":
         arr = (C.c_void_p * len(batches))(*[b.h for b in batches])

@@ -135,6 +135,10 @@ dfgpu_status dfgpu_batch_slice(dfgpu_ctx *ctx, const dfgpu_batch *batch, int64_t
  * expressions: physical-plan/src/projection.rs); columns share the input's device buffers */
 dfgpu_status dfgpu_batch_project(dfgpu_ctx *ctx, const dfgpu_batch *batch, const int32_t *cols, int32_t n_cols,
                                  dfgpu_batch **out);
+/* FilterExec: `batch_filter` -> arrow `filter_record_batch` (physical-plan/src/filter.rs:315-327).
+ * predicate_col is the Boolean column the predicate PhysicalExpr evaluated to; the output holds every column of the
+ * input (project afterwards) restricted to the rows where the predicate is true and not NULL, in input order. */
+dfgpu_status dfgpu_batch_filter(dfgpu_ctx *ctx, const dfgpu_batch *batch, int32_t predicate_col, dfgpu_batch **out);
 void dfgpu_batch_free(dfgpu_batch *batch);
 
 /* ---- create_hashes (common/src/hash_utils.rs:357-416) — test hook; seed 0 is the fixed

@@ -254,6 +254,18 @@ def partition_ids(key_cols: Sequence[pa.Array], n_parts: int) -> np.ndarray:
     return out
 
 
+def filter_batch(batch: pa.RecordBatch, predicate: int) -> pa.RecordBatch:
+    """FilterExec::batch_filter (physical-plan/src/filter.rs:315-327): arrow `filter_record_batch` keeps the rows whose
+    predicate is true; a NULL predicate counts as false (arrow-rs `prep_null_mask_filter`).  Row order is preserved.
+    Restated as an index list + take, row by row."""
+    m = batch.column(predicate)
+    if not pa.types.is_boolean(m.type):
+        raise OracleError("Internal: filter predicate is not Boolean")
+    keep = [i for i, v in enumerate(m.to_pylist()) if v is True]
+    idx = pa.array(keep, pa.int64())
+    return pa.record_batch([c.take(idx) for c in batch.columns], schema=batch.schema)
+
+
 def partition(batch: pa.RecordBatch, key_idx: Sequence[int], n_parts: int) -> List[Optional[pa.RecordBatch]]:
     """BatchPartitioner::partition (repartition/mod.rs:133-217): empty partitions are not produced."""
     ids = partition_ids([batch.column(i) for i in key_idx], n_parts)

@@ -97,3 +97,31 @@ def test_partial_exchange_final_virtual_ranks(ctx):
         finals.append(fin.emit())
     want = oracle_agg("single", shards, ["k", "s"], specs)
     assert_rows_equal(rows_of(finals), rows_of(want), key_cols=[0, 1])
+
+
+# ---- FilterExec::batch_filter on the device ----
+@pytest.mark.parametrize("n,p_true,p_null", [(0, 0.5, 0.1), (1, 1.0, 0.0), (31, 0.5, 0.2), (4097, 0.02, 0.0), (100_003, 0.9, 0.05),
+                                              (50_000, 0.0, 0.0), (50_000, 1.0, 0.0)])
+def test_filter_vs_oracle(n, p_true, p_null):
+    from gpu_helpers import random_keys, random_values
+    rng = np.random.default_rng(n + 3)
+    ctx = gpu_ctx()
+    cols = [random_values(rng, n, "int64", 0.1), random_keys(rng, n, "utf8", 50, 0.1), random_values(rng, n, "decimal", 0.0),
+            pa.array(rng.random(n) < 0.5, pa.bool_()), random_keys(rng, n, "dict_utf8", 20, 0.1),
+            pa.array(rng.random(n) < p_true, pa.bool_(), mask=(rng.random(n) < p_null) if p_null else None)]
+    b = pa.record_batch(cols, names=["i", "s", "d", "flag", "dict", "pred"])
+    # a sliced input: non-zero bit offsets on the predicate and the validity bitmaps
+    for batch in ([b] if n < 10 else [b, b.slice(5, n - 7)]):
+        got = df.DeviceBatch.from_arrow(ctx, batch).filter("pred").to_arrow()
+        want = oracle.filter_batch(batch, 5)
+        assert got.schema.types == want.schema.types
+        assert_rows_equal(rows_of(got), rows_of(want), ordered=True, what=f"filter n={n}")   # input order is preserved
+    ctx.close()
+
+
+def test_filter_rejects_non_boolean():
+    ctx = gpu_ctx()
+    b = pa.record_batch([pa.array([1, 2, 3], pa.int64())], names=["i"])
+    with pytest.raises(Exception, match="Boolean"):
+        df.DeviceBatch.from_arrow(ctx, b).filter("i")
+    ctx.close()
