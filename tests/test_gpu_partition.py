@@ -103,7 +103,7 @@ def test_partial_exchange_final_virtual_ranks(ctx):
 @pytest.mark.parametrize("n,p_true,p_null", [(0, 0.5, 0.1), (1, 1.0, 0.0), (31, 0.5, 0.2), (4097, 0.02, 0.0), (100_003, 0.9, 0.05),
                                               (50_000, 0.0, 0.0), (50_000, 1.0, 0.0)])
 def test_filter_vs_oracle(n, p_true, p_null):
-    from gpu_helpers import random_keys, random_values
+    import datafusion_upstream_b200 as df
     rng = np.random.default_rng(n + 3)
     ctx = gpu_ctx()
     cols = [random_values(rng, n, "int64", 0.1), random_keys(rng, n, "utf8", 50, 0.1), random_values(rng, n, "decimal", 0.0),
@@ -120,6 +120,7 @@ def test_filter_vs_oracle(n, p_true, p_null):
 
 
 def test_filter_rejects_non_boolean():
+    import datafusion_upstream_b200 as df
     ctx = gpu_ctx()
     b = pa.record_batch([pa.array([1, 2, 3], pa.int64())], names=["i"])
     with pytest.raises(Exception, match="Boolean"):
