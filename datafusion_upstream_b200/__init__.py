@@ -5,4 +5,4 @@ this package is the thin host-side mirror of the reference operator interface us
 """
 from ._native import DfGpuError, LIB_PATH, SYMBOLS  # noqa: F401
 from .exec import (AggFunc, AggregateExpr, AggregateMode, DeviceBatch, GpuAggregateExec, GpuContext,  # noqa: F401
-                   GpuHashJoinExec, GpuRepartitionExec, JoinType, PartitionMode, all_gather, create_hashes, slice_batches)
+                   GpuCoalesceBatchesExec, GpuHashJoinExec, GpuRepartitionExec, JoinType, PartitionMode, all_gather, create_hashes, slice_batches)

@@ -79,6 +79,7 @@ SYMBOLS = [
     "dfgpu_join_build_push", "dfgpu_join_build_finish", "dfgpu_join_probe", "dfgpu_join_emit_unmatched",
     "dfgpu_join_metrics", "dfgpu_join_destroy", "dfgpu_partition_hash", "dfgpu_exchange_all_to_all",
     "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter",
+    "dfgpu_coalescer_create", "dfgpu_coalescer_push", "dfgpu_coalescer_finish", "dfgpu_coalescer_destroy",
 ]
 
 _lib = None
@@ -119,6 +120,11 @@ def lib():
     L.dfgpu_agg_exchange.argtypes = [P]
     L.dfgpu_batch_project.argtypes = [P, P, C.POINTER(C.c_int32), C.c_int32, C.POINTER(P)]
     L.dfgpu_batch_filter.argtypes = [P, P, C.c_int32, C.POINTER(P)]
+    L.dfgpu_coalescer_create.argtypes = [P, P, C.c_int64, C.POINTER(P)]
+    L.dfgpu_coalescer_push.argtypes = [P, P, C.POINTER(P)]
+    L.dfgpu_coalescer_finish.argtypes = [P, C.POINTER(P)]
+    L.dfgpu_coalescer_destroy.argtypes = [P]
+    L.dfgpu_coalescer_destroy.restype = None
     L.dfgpu_batch_free.argtypes = [P]
     L.dfgpu_create_hashes.argtypes = [P, P, C.POINTER(C.c_int32), C.c_int32, C.c_uint64, P]
     L.dfgpu_agg_create.argtypes = [P, C.c_int32, P, C.POINTER(C.c_int32), C.c_int32, C.POINTER(AggDesc), C.c_int32, C.POINTER(P)]

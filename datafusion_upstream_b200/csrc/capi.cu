@@ -243,6 +243,54 @@ dfgpu_status dfgpu_batch_project(dfgpu_ctx *ctx, const dfgpu_batch *b, const int
     *out = o.release();
     DF_CATCH
 }
+struct dfgpu_coalescer {
+    dfgpu::CtxHold ctx;
+    dfgpu::Schema schema;
+    int64_t target = 0;
+    std::unique_ptr<dfgpu::HostCoalescer> co;
+};
+dfgpu_status dfgpu_coalescer_create(dfgpu_ctx *ctx, const ArrowSchema *schema, int64_t target_rows, dfgpu_coalescer **out) {
+    DF_TRY
+    if (!ctx || !schema || !out) fail(DFGPU_INTERNAL, "null argument");
+    if (target_rows <= 0) fail(DFGPU_PLAN, "CoalesceBatchesExec: target_batch_size must be positive");
+    DF_CUDA(cudaSetDevice(ctx->device));
+    std::unique_ptr<dfgpu_coalescer> c(new dfgpu_coalescer());
+    c->ctx = ctx;
+    c->schema = schema_from_arrow(schema);
+    c->target = target_rows;
+    if (!HostCoalescer::supports(c->schema))
+        fail(DFGPU_NOT_IMPLEMENTED, "This feature is not implemented: host batch coalescing of dictionary / nested columns");
+    c->co.reset(new HostCoalescer(ctx, c->schema, target_rows));
+    *out = c.release();
+    DF_CATCH
+}
+dfgpu_status dfgpu_coalescer_push(dfgpu_coalescer *c, const ArrowArray *batch, dfgpu_batch **out) {
+    DF_TRY
+    if (!c || !batch || !out) fail(DFGPU_INTERNAL, "null argument");
+    *out = nullptr;
+    Ctx *ctx = c->ctx;
+    DF_CUDA(cudaSetDevice(ctx->device));
+    if (batch->length >= c->target && c->co->rows() == 0) {  // coalesce_batches.rs:215-218
+        *out = batch_import(ctx, batch, c->schema, false);
+    } else if (batch->length > 0) {                          // :219-240
+        if (!c->co->fits(batch)) *out = c->co->flush();      // i32 Utf8 offsets would overflow: hand over early
+        c->co->append(batch);
+        if (!*out && c->co->rows() >= c->target) *out = c->co->flush();
+    }
+    DF_CATCH
+}
+dfgpu_status dfgpu_coalescer_finish(dfgpu_coalescer *c, dfgpu_batch **out) {
+    DF_TRY
+    if (!c || !out) fail(DFGPU_INTERNAL, "null argument");
+    DF_CUDA(cudaSetDevice(c->ctx->device));
+    *out = c->co->flush();                                   // :242-262 (nullptr when the buffer is empty)
+    DF_CATCH
+}
+void dfgpu_coalescer_destroy(dfgpu_coalescer *c) {
+    if (!c) return;
+    cudaSetDevice(c->ctx->device);
+    delete c;
+}
 dfgpu_status dfgpu_batch_filter(dfgpu_ctx *ctx, const dfgpu_batch *b, int32_t predicate_col, dfgpu_batch **out) {
     DF_TRY
     if (!b || !out) fail(DFGPU_INTERNAL, "null argument");

@@ -438,6 +438,57 @@ class GpuHashJoinExec:
             pass
 
 
+class GpuCoalesceBatchesExec:
+    """CoalesceBatchesExec (physical-plan/src/coalesce_batches.rs) at the PCIe boundary: host RecordBatches in, device
+    batches of >= target_batch_size rows out (the last one may be smaller).  Same buffering rule as the reference:
+    emit when buffered_rows >= target, pass a large batch through an empty buffer, drop empty batches."""
+
+    def __init__(self, ctx: GpuContext, schema: pa.Schema, target_batch_size: int):
+        self.ctx, self.schema, self.target_batch_size = ctx, schema, target_batch_size
+        s = N.export_schema(schema)
+        h = C.c_void_p()
+        try:
+            N.check(N.lib().dfgpu_coalescer_create(ctx.h, C.addressof(s), target_batch_size, C.byref(h)))
+        finally:
+            N.release_schema(s)
+        self.h = h
+
+    def push(self, batch: pa.RecordBatch) -> Optional[DeviceBatch]:
+        if batch.schema.types != self.schema.types:
+            raise N.DfGpuError(1, f"Internal error: pushed batch schema {batch.schema.types} != {self.schema.types}")
+        a, s = N.ArrowArray(), N.ArrowSchema()
+        batch._export_to_c(C.addressof(a), C.addressof(s))
+        out = C.c_void_p()
+        try:
+            N.check(N.lib().dfgpu_coalescer_push(self.h, C.addressof(a), C.byref(out)))
+        finally:
+            if a.release:
+                C.CFUNCTYPE(None, C.POINTER(N.ArrowArray))(a.release)(C.byref(a))
+            N.release_schema(s)
+        return DeviceBatch(self.ctx, out) if out.value else None
+
+    def finish(self) -> Optional[DeviceBatch]:
+        out = C.c_void_p()
+        N.check(N.lib().dfgpu_coalescer_finish(self.h, C.byref(out)))
+        return DeviceBatch(self.ctx, out) if out.value else None
+
+    def execute(self, batches: Sequence[pa.RecordBatch]) -> List[DeviceBatch]:
+        out = [d for d in (self.push(b) for b in batches) if d is not None]
+        last = self.finish()
+        return out + ([last] if last is not None else [])
+
+    def close(self):
+        if getattr(self, "h", None):
+            N.lib().dfgpu_coalescer_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class GpuRepartitionExec:
     """RepartitionExec with Partitioning::Hash(exprs, n) (repartition/mod.rs:295-580)."""
 

@@ -135,6 +135,19 @@ dfgpu_status dfgpu_batch_slice(dfgpu_ctx *ctx, const dfgpu_batch *batch, int64_t
  * expressions: physical-plan/src/projection.rs); columns share the input's device buffers */
 dfgpu_status dfgpu_batch_project(dfgpu_ctx *ctx, const dfgpu_batch *batch, const int32_t *cols, int32_t n_cols,
                                  dfgpu_batch **out);
+/* CoalesceBatchesExec (physical-plan/src/coalesce_batches.rs:205-262) at the PCIe boundary: host batches
+ * are packed into a pinned arena and leave as ONE device batch once `target_rows` rows are buffered
+ * (`buffered_rows >= target_batch_size`, :226); a batch of >= target_rows rows arriving at an empty buffer passes
+ * through (:215-218); empty batches are discarded (:219).  push sets *out to the finished batch or NULL; finish
+ * returns what is left (NULL when nothing is).  Inputs are borrowed for the duration of the call only.  Dictionary
+ * columns -> NotImplemented (a dictionary per batch cannot be packed). */
+typedef struct dfgpu_coalescer dfgpu_coalescer;
+dfgpu_status dfgpu_coalescer_create(dfgpu_ctx *ctx, const struct ArrowSchema *schema, int64_t target_rows,
+                                    dfgpu_coalescer **out);
+dfgpu_status dfgpu_coalescer_push(dfgpu_coalescer *c, const struct ArrowArray *batch, dfgpu_batch **out);
+dfgpu_status dfgpu_coalescer_finish(dfgpu_coalescer *c, dfgpu_batch **out);
+void dfgpu_coalescer_destroy(dfgpu_coalescer *c);
+
 /* FilterExec: `batch_filter` -> arrow `filter_record_batch` (physical-plan/src/filter.rs:315-327).
  * predicate_col is the Boolean column the predicate PhysicalExpr evaluated to; the output holds every column of the
  * input (project afterwards) restricted to the rows where the predicate is true and not NULL, in input order. */

@@ -126,3 +126,47 @@ def test_filter_rejects_non_boolean():
     with pytest.raises(Exception, match="Boolean"):
         df.DeviceBatch.from_arrow(ctx, b).filter("i")
     ctx.close()
+
+
+# ---- CoalesceBatchesExec at the PCIe boundary (dfgpu_coalescer_*) ----
+def test_coalesce_batches_golden():
+    """coalesce_batches.rs:298-316 (test_concat_batches): 10 batches x 8 rows, target 21 -> 24, 24, 24, 8 rows."""
+    import datafusion_upstream_b200 as df
+    ctx = gpu_ctx()
+    schema = pa.schema([pa.field("c0", pa.uint32(), nullable=False)])
+    b = pa.record_batch([pa.array([1, 2, 3, 4, 5, 6, 7, 8], pa.uint32())], schema=schema)
+    op = df.GpuCoalesceBatchesExec(ctx, schema, 21)
+    outs = [d.to_arrow() for d in op.execute([b] * 10)]
+    assert [o.num_rows for o in outs] == [24, 24, 24, 8]
+    assert all(o.column(0).to_pylist() == [1, 2, 3, 4, 5, 6, 7, 8] * (o.num_rows // 8) for o in outs)
+    op.close()
+    ctx.close()
+
+
+def test_coalesce_batches_vs_concat():
+    """Every column kind the arena packs, slices with odd offsets, pass-through of a large batch, empty batches dropped;
+    the concatenation of the outputs equals the concatenation of the inputs, row for row and in order."""
+    import datafusion_upstream_b200 as df
+    rng = np.random.default_rng(17)
+    ctx = gpu_ctx()
+    n = 30_000
+    whole = pa.record_batch([random_values(rng, n, "int64", 0.1), random_keys(rng, n, "utf8", 500, 0.1), random_values(rng, n, "decimal", 0.05),
+                             pa.array(rng.random(n) < 0.5, pa.bool_(), mask=rng.random(n) < 0.1), random_keys(rng, n, "large_utf8", 90, 0.0),
+                             random_values(rng, n, "int8", 0.0)], names=["i", "s", "d", "b", "ls", "t"])
+    lens = [5, 0, 1000, 17, 4000, 3, 3, 8192, 1, 2500, 9000, 11]
+    pieces, off = [], 0
+    while off < n:
+        for ln in lens:
+            ln = min(ln, n - off)
+            pieces.append(whole.slice(off, ln))
+            off += ln
+            if off >= n:
+                break
+    op = df.GpuCoalesceBatchesExec(ctx, whole.schema, 4096)
+    outs = [d.to_arrow() for d in op.execute(pieces)]
+    assert all(o.num_rows >= 4096 for o in outs[:-1]) and sum(o.num_rows for o in outs) == n
+    assert_rows_equal(rows_of(outs), rows_of(whole), ordered=True, what="coalesce")
+    op.close()
+    with pytest.raises(Exception, match="not implemented|NotImplemented"):
+        df.GpuCoalesceBatchesExec(ctx, pa.schema([("d", pa.dictionary(pa.int32(), pa.string()))]), 100)
+    ctx.close()
