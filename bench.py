@@ -262,7 +262,7 @@ def build_workload(args, df, ctx, torch, device, rank):
         w["cpu"] = cpu
     elif args.workload == "c5":
         region, offsets, data = gen_c5(n, 42 + rank, device)
-        schema = pa.schema([("RegionID", pa.int32()), ("SearchPhrase", pa.string())])
+        schema = pa.schema([pa.field("RegionID", pa.int32(), nullable=False), pa.field("SearchPhrase", pa.string(), nullable=False)])   # ClickBench hits: NOT NULL
         w["name"] = (f"ClickBench-shaped GROUP BY RegionID, SearchPhrase COUNT(*), {n} rows, Int32 x Utf8 keys (70% empty phrase, Zipf over "
                      f"6M phrases of 1-80 bytes, {int(data.numel())} string bytes) - variable-width GroupValues interning (BASELINE configs[4])")
         w["dev"] = df.DeviceBatch.from_device(ctx, schema, [{"buffers": [None, region.data_ptr()], "null_count": 0},

@@ -60,7 +60,7 @@ DF_D void fa_load_key(const FaPlan &pl, int64_t row, uint64_t &key, int &side) {
         key = 0;
         for (int k = 0; k < pl.nkeys; k++) {
             const FaKeyCol &kc = pl.keys[k];
-            if (!col_valid(kc.v, row)) {
+            if (kc.null_bit >= 0 && !col_valid(kc.v, row)) {
                 key |= 1ULL << (8 * pl.null_off + kc.null_bit);
                 continue;
             }

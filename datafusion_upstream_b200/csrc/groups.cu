@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(256) k_pack_keys(PackPlan p, int64_t n, uint8_
                 *(uint32_t *)(row + pc.off) = id;
                 continue;
             }
-            if (!col_valid(pc.v, i)) {
+            if (pc.null_bit >= 0 && !col_valid(pc.v, i)) {
                 any_null = true;
                 row[p.null_off + (pc.null_bit >> 3)] |= (uint8_t)(1u << (pc.null_bit & 7));
                 continue;

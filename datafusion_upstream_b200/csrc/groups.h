@@ -62,7 +62,9 @@ enum NullPolicy { NULLS_ARE_KEYS = 0, NULLS_EXCLUDED = 1 };
 
 class GroupTable {
   public:
-    GroupTable(Ctx *ctx, const std::vector<TypeInfo> &key_types);
+    // trust_nullability: columns declared NOT NULL get no null bit in the packed key image (arrow-rs rejects a batch
+    // with nulls in a non-nullable field, RecordBatch::try_new), so e.g. (Int32 NOT NULL, Utf8) packs into 64 bits
+    GroupTable(Ctx *ctx, const std::vector<TypeInfo> &key_types, bool trust_nullability = false);
     ~GroupTable();
 
     // Intern rows [0, n) of `cols` (one per key column, already sliced to the chunk).  Writes one
@@ -90,6 +92,9 @@ class GroupTable {
     int null_off() const { return null_off_; }
     // Take ownership of a dense key store produced elsewhere (U64 layouts only): emit_keys(G) then
     // reads these images.  null_gid = id of the NULL-key group of a DIRECT table, or -1.
+    // per-row ids of the Utf8/Binary key column `c` of a packed layout (interned in that column's own table;
+    // STRID_NULL for NULL): lets the two-level path treat the column as a 4-byte field of the key image
+    BufRef string_field_ids(size_t c, const DevCol &col, int64_t row_off, int64_t n) { return string_ids(cols_[c], col, row_off, n, false); }
     void adopt_dense(const BufRef &keys, int64_t null_gid) {
         gkeys_ = keys;
         tv_.gkeys = keys ? keys->as<uint64_t>() : nullptr;

@@ -16,7 +16,20 @@ from util import assert_rows_equal, assert_tables_equal, rows_of
 pytestmark = pytest.mark.gpu
 
 # everything the two-level path supports: MIN/MAX over Decimal128 (128-bit CAS state) stays on the table path
-FAST_SPECS = [s for s in SPECS if not (s[0] in ("min", "max") and s[1] in ("d", "big"))]
+# and the operator takes the path only with <= 24 state ops (FA_MAX_OPS; AVG = 2 ops): AVG(s) is left out to stay within it
+FAST_SPECS = [s for s in SPECS if not (s[0] in ("min", "max") and s[1] in ("d", "big")) and s[:2] != ("avg", "s")]
+assert sum(2 if s[0] == "avg" else 1 for s in FAST_SPECS) <= 24
+
+
+def ran_two_level(c, fn):
+    """Run fn() with kernel profiling on and report whether any two-level kernel (k_fa_l1 / k_fa_l1_reg / k_fa_l2) ran."""
+    c.set_profiling(True)
+    try:
+        out = fn()
+        names = {r["name"] for r in c.profile()}
+    finally:
+        c.set_profiling(False)
+    return out, any(n.startswith("k_fa_l") for n in names), sorted(names)
 FAST_KEYS = [["int64"], ["int64_small"], ["uint64"], ["int32"], ["int16", "int8"], ["float32"], ["date32"], ["timestamp"],
              ["uint8", "uint8"], ["int32", "int16", "bool"], ["bool"], ["float64"]]
 
@@ -46,7 +59,8 @@ def test_single_vs_oracle(ctx, monkeypatch, keys, card, hook):
     nulls = card != 37
     batches = [make_table(rng, n, keys, card, 0.1 if nulls else 0.0, 0.15 if nulls else 0.0) for n in (3000, 1, 0, 9001)]
     gk = [f"k{i}" for i in range(len(keys))]
-    got = gpu_agg(ctx, "single", batches, gk, FAST_SPECS)
+    got, fast, names = ran_two_level(ctx, lambda: gpu_agg(ctx, "single", batches, gk, FAST_SPECS))
+    assert fast == (hook != "table_path"), f"path taken: {names}"      # the library picks the path; make sure it is the one under test
     want = oracle_agg("single", batches, gk, FAST_SPECS)
     assert_tables_equal(got, want, key_cols=list(range(len(keys))), what=f"{keys} card={card} {hook}")
 
@@ -193,3 +207,67 @@ def test_clickbench_shape_properties_at_scale(ctx, dist):
     assert len(np.unique(k)) == len(k) == len(np.unique(keys))
     with np.errstate(over="ignore"):
         assert (k.view(np.uint64) * c.astype(np.uint64)).sum() == keys.view(np.uint64).sum()
+
+
+# ---- Utf8 / Binary key columns as 4-byte string-id fields of the key image; NOT NULL columns carry no null bit ----
+def _with_nullability(batch, not_null):
+    """Re-declare the listed columns NOT NULL (they hold no nulls)."""
+    fields = [pa.field(f.name, f.type, nullable=f.name not in not_null) for f in batch.schema]
+    return pa.record_batch(batch.columns, schema=pa.schema(fields))
+
+
+STRING_KEYS = [
+    (["int32", "utf8"], ["k0"]),             # ClickBench (RegionID NOT NULL, SearchPhrase): 4 + 4 bytes, no null bit
+    (["utf8", "utf8"], []),                  # two string ids, NULL encoded inside each field
+    (["int16", "large_utf8", "int8"], ["k0", "k2"]),
+    (["binary", "int32"], ["k1"]),
+    (["int32", "int16"], ["k0", "k1"]),      # no strings: NOT NULL only changes the image layout
+]
+
+
+@pytest.mark.parametrize("hook", ["default", "tiny_tables", "always_partition", "table_path"])
+@pytest.mark.parametrize("card", [5, 3000], ids=lambda c: f"card{c}")
+@pytest.mark.parametrize("keys,not_null", STRING_KEYS, ids=["+".join(k) for k, _ in STRING_KEYS])
+def test_string_id_fields_vs_oracle(monkeypatch, keys, not_null, card, hook):
+    for k, v in HOOKS[hook].items():
+        monkeypatch.setenv(k, v)
+    c = gpu_ctx()
+    try:
+        rng = np.random.default_rng(sum(map(ord, "".join(keys))) + card + 1)
+        batches = []
+        for n in (4000, 1, 0, 12_001):
+            cols, names = [], []
+            for i, k in enumerate(keys):
+                cols.append(random_keys(rng, n, k, card, 0.0 if f"k{i}" in not_null else 0.1))
+                names.append(f"k{i}")
+            t = make_table(rng, n, ["int8"], 3, 0.0, 0.15)           # value / filter columns
+            b = pa.record_batch(cols + t.columns[1:], names=names + t.schema.names[1:])
+            batches.append(_with_nullability(b, not_null))
+        gk = [f"k{i}" for i in range(len(keys))]
+        got, fast, names = ran_two_level(c, lambda: gpu_agg(c, "single", batches, gk, FAST_SPECS))
+        assert fast == (hook != "table_path"), f"path taken: {names}"
+        want = oracle_agg("single", batches, gk, FAST_SPECS)
+        assert_tables_equal(got, want, key_cols=list(range(len(keys))), what=f"{keys} card={card} {hook}")
+        assert [f.nullable for f in got.schema][:len(keys)] == [f"k{i}" not in not_null for i in range(len(keys))]
+        # Partial per partition -> FinalPartitioned (state batches keep the key fields' nullability)
+        parts = [batches[:1], batches[1:]]
+        states = [gpu_agg(c, "partial", p, gk, FAST_SPECS) for p in parts]
+        fin = [(f, None, n, None) for f, _, n, _ in FAST_SPECS]
+        got2 = gpu_agg(c, "final_partitioned", states, list(range(len(keys))), fin)
+        assert_rows_equal(rows_of(got2), rows_of(want), key_cols=list(range(len(keys))))
+    finally:
+        c.close()
+
+
+def test_string_keys_refuse_record_exchange():
+    """String ids are local to a rank's interner: the fused record exchange must refuse (the caller keeps the
+    three-operator plan), before any communication."""
+    import datafusion_upstream_b200 as df
+    c = gpu_ctx()
+    b = pa.record_batch([pa.array([1, 2], pa.int32()), pa.array(["a", "b"])], names=["r", "s"])
+    op = df.GpuAggregateExec(c, df.AggregateMode.Single, b.schema, ["r", "s"], [df.AggregateExpr(df.AggFunc.Count, None, "c")])
+    op.push(b)
+    op.exchange()       # world == 1: nothing to exchange, no error
+    assert op.emit().num_rows == 2
+    op.close()
+    c.close()
