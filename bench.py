@@ -346,7 +346,7 @@ def run_ours(args):
         dist.broadcast_object_list(box, src=0)
         uid = box[0]
     with native_stdout_to_stderr():
-        ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid, coalesce_rows=args.coalesce_rows)
+        ctx = df.GpuContext(device=local, rank=rank, world=world, nccl_unique_id=uid, coalesce_rows=args.coalesce_rows, chunk_rows=args.chunk_rows)
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
     w = build_workload(args, df, ctx, torch, device, rank)
     n = args.rows
@@ -946,6 +946,7 @@ def main():
     ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--batch-rows", type=int, default=0, help="e2e leg: push the host batch in slices of this many rows (8192 = the reference's batch_size)")
+    ap.add_argument("--chunk-rows", type=int, default=0, help="dfgpu_options.chunk_rows (rows per internal launch wave; 0 = default)")
     ap.add_argument("--coalesce-rows", type=int, default=0, help="dfgpu_options.coalesce_rows (0 = default 1 Mi, -1 = off)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--three-op", action="store_true", help="N > 1: Partial -> partition -> all-to-all -> FinalPartitioned as three operators instead of the fused record exchange")
