@@ -260,7 +260,7 @@ def build_workload(args, df, ctx, torch, device, rank):
             d = [cols[c][:sample].cpu().numpy() for c in ("qty", "price", "disc_price", "charge", "disc")]
             return oracle.bench_q1(f, s, d, threads)
         w["cpu"] = cpu
-    elif args.workload == "c5":
+    elif args.workload in ("c5", "c5s"):
         region, offsets, data = gen_c5(n, 42 + rank, device)
         schema = pa.schema([pa.field("RegionID", pa.int32(), nullable=False), pa.field("SearchPhrase", pa.string(), nullable=False)])   # ClickBench hits: NOT NULL
         w["name"] = (f"ClickBench-shaped GROUP BY RegionID, SearchPhrase COUNT(*), {n} rows, Int32 x Utf8 keys (70% empty phrase, Zipf over "
@@ -272,6 +272,10 @@ def build_workload(args, df, ctx, torch, device, rank):
         w["group_by"] = ["RegionID", "SearchPhrase"]
         w["exprs"] = [df.AggregateExpr(df.AggFunc.Count, None, "COUNT(*)")]
         w["in_bytes"] = 4 * n + 4 * (n + 1) + int(data.numel())
+        if args.workload == "c5s":      # the single-key variant: GROUP BY SearchPhrase (GroupValuesByes, bytes.rs:44-121)
+            w["name"] = w["name"].replace("GROUP BY RegionID, SearchPhrase", "GROUP BY SearchPhrase").replace("Int32 x Utf8 keys", "one Utf8 key")
+            w["group_by"] = ["SearchPhrase"]
+            w["in_bytes"] -= 4 * n
         w["out_row_bytes"] = 4 + 4 + 8          # RegionID + phrase offset + count (the distinct phrases' own bytes are not counted)
         host_cols = [("RegionID", pa.int32(), region), ("SearchPhrase", pa.string(), (offsets, data))]
 
@@ -515,7 +519,7 @@ def run_ours(args):
         line = {
             "metric": "input rows/s (hash aggregation, device-resident input) and HBM GB/s", "value": value, "unit": "rows/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": {"c2": "int64", "c5": "u8"}.get(args.workload, "i128"), "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": {"c2": "int64", "c5": "u8", "c5s": "u8"}.get(args.workload, "i128"), "data": "synthetic",
             "config": {"workload": w["name"], "rows_per_gpu": n, "groups": groups, "l2_policy": "inputs larger than L2 (no flush needed)"
                        if w["in_bytes"] > 256e6 else "inputs smaller than L2: table/state reset each step", "mode": "Single" if world == 1 else
                        (f"Partial -> NCCL all-to-all -> FinalPartitioned (dp{world})" if args.three_op else
@@ -940,7 +944,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--workload", default="c2", choices=["c2", "q1", "join", "q3", "c5"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "q1", "join", "q3", "c5", "c5s"])
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=50_000_000)
     ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
@@ -952,10 +956,10 @@ def main():
     ap.add_argument("--three-op", action="store_true", help="N > 1: Partial -> partition -> all-to-all -> FinalPartitioned as three operators instead of the fused record exchange")
     args = ap.parse_args()
     if args.rows <= 0:
-        args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000, "q3": 10, "c5": 100_000_000}[args.workload]   # q3: --rows = scale factor
+        args.rows = {"c2": 100_000_000, "q1": 60_012_150, "join": 32_400_000, "q3": 10, "c5": 100_000_000, "c5s": 100_000_000}[args.workload]   # q3: --rows = scale factor
     if args.warmup < 3 and args.impl != "reference":
         args.warmup = max(args.warmup, 3)       # timing rules: W >= 3
-    if args.workload == "c5":
+    if args.workload in ("c5", "c5s"):
         args.three_op = True     # string keys: the fused record exchange covers 64-bit key images only
     if args.impl == "reference":
         run_reference(args)

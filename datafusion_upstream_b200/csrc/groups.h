@@ -64,7 +64,9 @@ class GroupTable {
   public:
     // trust_nullability: columns declared NOT NULL get no null bit in the packed key image (arrow-rs rejects a batch
     // with nulls in a non-nullable field, RecordBatch::try_new), so e.g. (Int32 NOT NULL, Utf8) packs into 64 bits
-    GroupTable(Ctx *ctx, const std::vector<TypeInfo> &key_types, bool trust_nullability = false);
+    // pack_single_string: a lone Utf8/Binary key is laid out as a packed image holding its 4-byte string id (interned
+    // in the column's own table) instead of KM_VAR, which makes it eligible for the two-level aggregation path
+    GroupTable(Ctx *ctx, const std::vector<TypeInfo> &key_types, bool trust_nullability = false, bool pack_single_string = false);
     ~GroupTable();
 
     // Intern rows [0, n) of `cols` (one per key column, already sliced to the chunk).  Writes one

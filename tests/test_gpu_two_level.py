@@ -222,6 +222,9 @@ STRING_KEYS = [
     (["int16", "large_utf8", "int8"], ["k0", "k2"]),
     (["binary", "int32"], ["k1"]),
     (["int32", "int16"], ["k0", "k1"]),      # no strings: NOT NULL only changes the image layout
+    (["utf8"], []),                          # a lone string key: packed image = its string id
+    (["large_utf8"], ["k0"]),
+    (["binary"], []),
 ]
 
 
