@@ -240,9 +240,20 @@ def build_workload(args, df, ctx, torch, device, rank):
         schema = pa.schema([("l_returnflag", pa.uint8()), ("l_linestatus", pa.uint8()), ("l_quantity", d152), ("l_extendedprice", d152),
                             ("l_discount", d152), ("disc_price", d384), ("charge", d386)])
         w["name"] = f"TPC-H Q1-shaped aggregation, {n} rows, 4 groups, 2xUInt8 keys, Decimal128 SUMx4 AVGx3 COUNT(*) (82 B/row variant of configs[0])"
+        if args.q1_keys == "utf8":
+            # configs[0] as written: l_returnflag / l_linestatus are Utf8 (one byte each) - the same bytes as the UInt8 variant
+            # behind i32 offsets 0..n (90 B/row)
+            offs = torch.arange(0, n + 1, device=device, dtype=torch.int32)
+            schema = pa.schema([pa.field("l_returnflag", pa.string(), nullable=False), pa.field("l_linestatus", pa.string(), nullable=False)] + list(schema)[2:])
+            w["name"] = w["name"].replace("2xUInt8 keys", "2xUtf8 keys (1 byte each)").replace("82 B/row variant of configs[0]", "configs[0] shape, 90 B/row")
         order = ["qty", "price", "disc", "disc_price", "charge"]
         bufs = [{"buffers": [None, flag.data_ptr()]}, {"buffers": [None, status.data_ptr()]}] + [{"buffers": [None, cols[c].data_ptr()]} for c in order]
-        w["dev"] = df.DeviceBatch.from_device(ctx, schema, bufs, n, keep=(flag, status, cols))
+        keep_offs = None
+        if args.q1_keys == "utf8":
+            bufs[0] = {"buffers": [None, offs.data_ptr(), flag.data_ptr()]}
+            bufs[1] = {"buffers": [None, offs.data_ptr(), status.data_ptr()]}
+            keep_offs = offs
+        w["dev"] = df.DeviceBatch.from_device(ctx, schema, bufs, n, keep=(flag, status, cols, keep_offs))
         w["schema"] = schema
         w["group_by"] = ["l_returnflag", "l_linestatus"]
         A = df.AggregateExpr
@@ -250,9 +261,11 @@ def build_workload(args, df, ctx, torch, device, rank):
                       A(df.AggFunc.Sum, "disc_price", "sum_disc_price"), A(df.AggFunc.Sum, "charge", "sum_charge"),
                       A(df.AggFunc.Avg, "l_quantity", "avg_qty"), A(df.AggFunc.Avg, "l_extendedprice", "avg_price"),
                       A(df.AggFunc.Avg, "l_discount", "avg_disc"), A(df.AggFunc.Count, None, "count_order")]
-        w["in_bytes"] = 82 * n
+        w["in_bytes"] = (90 if args.q1_keys == "utf8" else 82) * n
         w["out_row_bytes"] = 0
-        host_cols = [("l_returnflag", pa.uint8(), flag), ("l_linestatus", pa.uint8(), status)] + \
+        kcols = [("l_returnflag", pa.string(), (offs, flag)), ("l_linestatus", pa.string(), (offs, status))] if args.q1_keys == "utf8" else \
+                [("l_returnflag", pa.uint8(), flag), ("l_linestatus", pa.uint8(), status)]
+        host_cols = kcols + \
                     [(nm, t, cols[c]) for (nm, t), c in zip(list(zip(schema.names, schema.types))[2:], order)]
 
         def cpu(threads, sample):
@@ -950,6 +963,7 @@ def main():
     ap.add_argument("--clocks", default="nvml", choices=["nvml", "smi", "off"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--batch-rows", type=int, default=0, help="e2e leg: push the host batch in slices of this many rows (8192 = the reference's batch_size)")
+    ap.add_argument("--q1-keys", default="u8", choices=["u8", "utf8"], help="q1: key columns as 2 x UInt8 (default) or 2 x Utf8 as in configs[0]")
     ap.add_argument("--chunk-rows", type=int, default=0, help="dfgpu_options.chunk_rows (rows per internal launch wave; 0 = default)")
     ap.add_argument("--coalesce-rows", type=int, default=0, help="dfgpu_options.coalesce_rows (0 = default 1 Mi, -1 = off)")
     ap.add_argument("--no-cpu", action="store_true")

@@ -113,6 +113,7 @@ class GroupTable {
         std::unique_ptr<GroupTable> strs;  // per-column string interner (kind 2)
     };
     void ensure(int64_t n, int64_t var_bytes);
+    void note_inserts();
     void grow(uint64_t new_max);
     void alloc_table(uint64_t new_max);
     BufRef string_ids(KeyCol &kc, const DevCol &col, int64_t row_off, int64_t n, bool find_only);
@@ -125,6 +126,13 @@ class GroupTable {
     BufRef slots_, gkeys_, grows_, heap_, goff_, glen_, scalars_;  // scalars: ngroups, overflow, heap_used
     int64_t groups_ub_ = 0;
     int64_t heap_cap_ = 0, heap_ub_ = 0;
+    // Lagged exact counters: after every inserting intern launch the 16 bytes of device scalars (group count, overflow
+    // flag, heap bytes) are copied to pinned host memory and an event is recorded.  ensure() then waits for THAT event
+    // only - not for the kernels queued behind it (level 1 of the same chunk, accumulate) - so the host can prepare
+    // the next chunk while the device still works on this one.  Nothing but intern kernels changes these counters.
+    uint32_t *count_host_ = nullptr;   // pinned: [0] groups, [1] overflow, [2..3] heap bytes used
+    cudaEvent_t count_ev_ = nullptr;
+    bool count_pending_ = false;
     bool adopted_ = false;
     int64_t adopted_null_gid_ = -1;
 };

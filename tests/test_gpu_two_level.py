@@ -225,6 +225,8 @@ STRING_KEYS = [
     (["utf8"], []),                          # a lone string key: packed image = its string id
     (["large_utf8"], ["k0"]),
     (["binary"], []),
+    (["dict_utf8"], []),                     # Dictionary(Int32, Utf8): the dictionary is interned once per batch
+    (["dict_utf8", "int32"], ["k1"]),
 ]
 
 
