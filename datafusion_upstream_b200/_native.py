@@ -54,6 +54,11 @@ class Options(C.Structure):
     ]
 
 
+class ExprNode(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("column", C.c_int32), ("left", C.c_int32), ("right", C.c_int32),
+                ("lit_lo", C.c_uint64), ("lit_hi", C.c_uint64), ("lit_precision", C.c_int32), ("lit_scale", C.c_int32)]
+
+
 class AggDesc(C.Structure):
     _fields_ = [("func", C.c_int32), ("name", C.c_char_p), ("arg_col", C.c_int32), ("filter_col", C.c_int32)]
 
@@ -78,7 +83,7 @@ SYMBOLS = [
     "dfgpu_agg_emit_arrow", "dfgpu_agg_metrics", "dfgpu_agg_destroy", "dfgpu_join_create", "dfgpu_join_output_schema",
     "dfgpu_join_build_push", "dfgpu_join_build_finish", "dfgpu_join_probe", "dfgpu_join_emit_unmatched",
     "dfgpu_join_metrics", "dfgpu_join_destroy", "dfgpu_partition_hash", "dfgpu_exchange_all_to_all",
-    "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter",
+    "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter", "dfgpu_batch_eval_decimal",
     "dfgpu_coalescer_create", "dfgpu_coalescer_push", "dfgpu_coalescer_finish", "dfgpu_coalescer_destroy",
 ]
 
@@ -120,6 +125,7 @@ def lib():
     L.dfgpu_agg_exchange.argtypes = [P]
     L.dfgpu_batch_project.argtypes = [P, P, C.POINTER(C.c_int32), C.c_int32, C.POINTER(P)]
     L.dfgpu_batch_filter.argtypes = [P, P, C.c_int32, C.POINTER(P)]
+    L.dfgpu_batch_eval_decimal.argtypes = [P, P, C.POINTER(ExprNode), C.c_int32, C.c_char_p, C.POINTER(P)]
     L.dfgpu_coalescer_create.argtypes = [P, P, C.c_int64, C.POINTER(P)]
     L.dfgpu_coalescer_push.argtypes = [P, P, C.POINTER(P)]
     L.dfgpu_coalescer_finish.argtypes = [P, C.POINTER(P)]

@@ -1317,4 +1317,169 @@ Batch *batch_filter(Ctx *ctx, const Batch *b, int predicate_col) {
 }
 }  // namespace dfgpu
 
+
+// ------------------------------------------------------------------------------------------------
+// ProjectionExec arithmetic over Decimal128 (dfgpu_batch_eval_decimal, include/dfgpu.h): one thread per row walks the
+// post-order node list; the result types and the 10^k rescale factors of + / - are resolved on the host.
+// ------------------------------------------------------------------------------------------------
+namespace dfgpu {
+static const int EX_MAX_NODES = 16;
+struct ExNode {
+    int32_t kind, left, right, pad;
+    ColView col;                 // COLUMN
+    uint64_t lit_lo, lit_hi;     // LITERAL
+    uint64_t lmul_lo, lmul_hi, rmul_lo, rmul_hi;  // ADD / SUB: 10^(scale - s_left), 10^(scale - s_right)
+};
+struct ExPlan {
+    int32_t n, pad;
+    ExNode nodes[EX_MAX_NODES];
+};
+DF_D bool mul128_checked(__int128 a, __int128 b, __int128 &r) {
+    if (a == 0 || b == 0) { r = 0; return true; }
+    const bool neg = (a < 0) != (b < 0);
+    const unsigned __int128 ua = a < 0 ? (unsigned __int128)(-(a + 1)) + 1 : (unsigned __int128)a;
+    const unsigned __int128 ub = b < 0 ? (unsigned __int128)(-(b + 1)) + 1 : (unsigned __int128)b;
+    const unsigned __int128 lim = neg ? ((unsigned __int128)1 << 127) : (((unsigned __int128)1 << 127) - 1);
+    if (ua > lim / ub) return false;
+    const unsigned __int128 m = ua * ub;
+    r = neg ? (__int128)(~m + 1) : (__int128)m;
+    return true;
+}
+DF_D bool add128_checked(__int128 a, __int128 b, __int128 &r) {
+    const unsigned __int128 s = (unsigned __int128)a + (unsigned __int128)b;
+    r = (__int128)s;
+    return !((a >= 0) == (b >= 0) && (r >= 0) != (a >= 0));
+}
+__global__ void __launch_bounds__(256) k_eval_decimal(ExPlan pl, int64_t n, uint64_t *__restrict__ out, uint32_t *__restrict__ valid_words,
+                                                      uint32_t *__restrict__ err) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t nround = (n + 31) / 32 * 32;
+    for (; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+        __int128 v[EX_MAX_NODES];
+        bool ok[EX_MAX_NODES];
+        bool valid = false;
+        if (i < n) {
+            for (int k = 0; k < pl.n; k++) {
+                const ExNode &nd = pl.nodes[k];
+                if (nd.kind == DFGPU_EXPR_COLUMN) {
+                    ok[k] = col_valid(nd.col, i);
+                    const uint64_t *p = (const uint64_t *)nd.col.values + 2 * i;
+                    v[k] = ok[k] ? (__int128)(((unsigned __int128)p[1] << 64) | p[0]) : 0;
+                } else if (nd.kind == DFGPU_EXPR_LITERAL) {
+                    ok[k] = true;
+                    v[k] = (__int128)(((unsigned __int128)nd.lit_hi << 64) | nd.lit_lo);
+                } else {
+                    ok[k] = ok[nd.left] && ok[nd.right];
+                    v[k] = 0;
+                    if (ok[k]) {
+                        bool fine;
+                        if (nd.kind == DFGPU_EXPR_MUL) {
+                            fine = mul128_checked(v[nd.left], v[nd.right], v[k]);
+                        } else {
+                            __int128 a, b;
+                            fine = mul128_checked(v[nd.left], (__int128)(((unsigned __int128)nd.lmul_hi << 64) | nd.lmul_lo), a) &&
+                                   mul128_checked(v[nd.right], (__int128)(((unsigned __int128)nd.rmul_hi << 64) | nd.rmul_lo), b);
+                            if (fine && nd.kind == DFGPU_EXPR_SUB) {
+                                if (b == (__int128)((unsigned __int128)1 << 127)) fine = add128_checked(a, 1, a) && add128_checked(a, -(b + 1), v[k]);  // a - MIN
+                                else fine = add128_checked(a, -b, v[k]);
+                            } else if (fine) {
+                                fine = add128_checked(a, b, v[k]);
+                            }
+                        }
+                        if (!fine) { atomicExch(err, 1u); v[k] = 0; }
+                    }
+                }
+            }
+            valid = ok[pl.n - 1];
+            const unsigned __int128 r = (unsigned __int128)v[pl.n - 1];
+            out[2 * i] = (uint64_t)r;
+            out[2 * i + 1] = (uint64_t)(r >> 64);
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, valid);
+        if ((threadIdx.x & 31) == 0) valid_words[i >> 5] = m;
+    }
+}
+
+Batch *batch_eval_decimal(Ctx *ctx, const Batch *b, const dfgpu_expr_node *nodes, int n_nodes, const char *name) {
+    if (!nodes || n_nodes <= 0) fail(DFGPU_PLAN, "eval: empty expression");
+    if (n_nodes > EX_MAX_NODES) fail(DFGPU_NOT_IMPLEMENTED, "This feature is not implemented: expressions with more than 16 nodes");
+    ExPlan pl;
+    memset(&pl, 0, sizeof pl);
+    pl.n = n_nodes;
+    int prec[EX_MAX_NODES], scale[EX_MAX_NODES];
+    auto pow10 = [](int e) { unsigned __int128 r = 1; for (int k = 0; k < e; k++) r *= 10; return r; };
+    bool any_nullable = false;
+    for (int k = 0; k < n_nodes; k++) {
+        const dfgpu_expr_node &s = nodes[k];
+        ExNode &d = pl.nodes[k];
+        d.kind = s.kind;
+        if (s.kind == DFGPU_EXPR_COLUMN) {
+            if (s.column < 0 || s.column >= (int)b->cols.size()) fail(DFGPU_PLAN, "eval: column index out of range");
+            const DevCol &c = *b->cols[(size_t)s.column];
+            if (c.type.id != T_DEC128) fail(DFGPU_NOT_IMPLEMENTED, "This feature is not implemented: decimal arithmetic over " + c.type.describe());
+            d.col = c.view();
+            prec[k] = c.type.precision; scale[k] = c.type.scale;
+            any_nullable = any_nullable || c.validity != nullptr;
+        } else if (s.kind == DFGPU_EXPR_LITERAL) {
+            d.lit_lo = s.lit_lo; d.lit_hi = s.lit_hi;
+            prec[k] = s.lit_precision; scale[k] = s.lit_scale;
+            if (prec[k] < 1 || prec[k] > 38 || scale[k] < 0 || scale[k] > prec[k]) fail(DFGPU_PLAN, "eval: invalid Decimal128 literal type");
+        } else if (s.kind == DFGPU_EXPR_ADD || s.kind == DFGPU_EXPR_SUB || s.kind == DFGPU_EXPR_MUL) {
+            if (s.left < 0 || s.left >= k || s.right < 0 || s.right >= k) fail(DFGPU_PLAN, "eval: operands must precede their operator (post order)");
+            d.left = s.left; d.right = s.right;
+            const int p1 = prec[s.left], s1 = scale[s.left], p2 = prec[s.right], s2 = scale[s.right];
+            if (s.kind == DFGPU_EXPR_MUL) {
+                if (s1 + s2 > 38)
+                    fail(DFGPU_EXECUTION, "Arrow error: Invalid argument error: Output scale of Decimal128(" + std::to_string(p1) + ", " + std::to_string(s1) +
+                                              ") * Decimal128(" + std::to_string(p2) + ", " + std::to_string(s2) + ") would exceed max scale of 38");
+                prec[k] = std::min(38, p1 + p2 + 1);
+                scale[k] = s1 + s2;
+            } else {
+                scale[k] = std::max(s1, s2);
+                prec[k] = std::min(38, scale[k] + std::max(p1 - s1, p2 - s2) + 1);
+                unsigned __int128 lm = pow10(scale[k] - s1), rm = pow10(scale[k] - s2);
+                d.lmul_lo = (uint64_t)lm; d.lmul_hi = (uint64_t)(lm >> 64);
+                d.rmul_lo = (uint64_t)rm; d.rmul_hi = (uint64_t)(rm >> 64);
+            }
+        } else {
+            fail(DFGPU_PLAN, "eval: unknown expression node kind");
+        }
+    }
+    const int64_t n = b->num_rows;
+    cudaStream_t st = ctx->stream;
+    auto col = std::make_shared<DevCol>();
+    col->type = make_type(T_DEC128, name ? name : "", true, prec[n_nodes - 1], scale[n_nodes - 1]);
+    col->length = n;
+    BufRef vals = make_buf(ctx, (size_t)n * 16 + 16), valid = make_buf(ctx, (size_t)((n + 31) / 32) * 4 + 16, true);
+    BufRef err = make_buf(ctx, 4, true);
+    col->owned.push_back(vals);
+    col->owned.push_back(valid);
+    col->values = vals->ptr;
+    col->validity = valid->as<uint8_t>();
+    col->null_count = any_nullable ? -1 : 0;
+    if (n > 0) {
+        int64_t abytes = n * 16;
+        for (int k = 0; k < n_nodes; k++)
+            if (nodes[k].kind == DFGPU_EXPR_COLUMN) abytes += n * 16;
+        {
+            KTimer kt(ctx, "k_eval_decimal", abytes);
+            k_eval_decimal<<<grid_for(n, 256, ctx, 16), 256, 0, st>>>(pl, n, vals->as<uint64_t>(), valid->as<uint32_t>(), err->as<uint32_t>());
+        }
+        note_launch(ctx);
+        DF_CUDA(cudaGetLastError());
+        uint32_t e = 0;
+        DF_CUDA(cudaMemcpyAsync(&e, err->ptr, 4, cudaMemcpyDeviceToHost, st));
+        DF_CUDA(cudaStreamSynchronize(st));
+        if (e) fail(DFGPU_EXECUTION, "Arrow error: Compute error: Overflow happened on a Decimal128 operation");
+    }
+    if (!any_nullable) { col->validity = nullptr; }
+    std::unique_ptr<Batch> o(new Batch());
+    o->ctx = ctx;
+    o->num_rows = n;
+    o->cols = b->cols;
+    o->cols.push_back(col);
+    return o.release();
+}
+}  // namespace dfgpu
+
 #include "coalesce.inc"

@@ -291,6 +291,14 @@ void dfgpu_coalescer_destroy(dfgpu_coalescer *c) {
     cudaSetDevice(c->ctx->device);
     delete c;
 }
+dfgpu_status dfgpu_batch_eval_decimal(dfgpu_ctx *ctx, const dfgpu_batch *b, const dfgpu_expr_node *nodes, int32_t n_nodes, const char *name,
+                                      dfgpu_batch **out) {
+    DF_TRY
+    if (!ctx || !b || !out) fail(DFGPU_INTERNAL, "null argument");
+    DF_CUDA(cudaSetDevice(ctx->device));
+    *out = batch_eval_decimal(ctx, b, nodes, n_nodes, name);
+    DF_CATCH
+}
 dfgpu_status dfgpu_batch_filter(dfgpu_ctx *ctx, const dfgpu_batch *b, int32_t predicate_col, dfgpu_batch **out) {
     DF_TRY
     if (!b || !out) fail(DFGPU_INTERNAL, "null argument");

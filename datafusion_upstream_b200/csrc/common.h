@@ -325,7 +325,8 @@ class HostCoalescer {
     int cur_ = 0;
 };
 Batch *batch_slice(Ctx *ctx, const Batch *b, int64_t off, int64_t len);
-Batch *batch_filter(Ctx *ctx, const Batch *b, int predicate_col);  // FilterExec::batch_filter (filter.rs:315-327)
+Batch *batch_filter(Ctx *ctx, const Batch *b, int predicate_col);
+Batch *batch_eval_decimal(Ctx *ctx, const Batch *b, const dfgpu_expr_node *nodes, int n_nodes, const char *name);  // FilterExec::batch_filter (filter.rs:315-327)
 // gather rows (compute::take); idx < 0 => NULL row.  idx is a device array of n int64.
 ColRef col_take(Ctx *ctx, const DevCol &src, const int64_t *idx, int64_t n, bool idx_may_be_null);
 // the same for several columns (each with its own index array): plain fixed-width columns share one launch

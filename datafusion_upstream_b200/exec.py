@@ -200,6 +200,27 @@ class DeviceBatch:
         N.check(N.lib().dfgpu_batch_project(self.ctx.h, self.h, (C.c_int32 * max(1, len(idx)))(*idx), len(idx), C.byref(h)))
         return DeviceBatch(self.ctx, h, keep=self)
 
+    def eval_decimal(self, nodes: Sequence[tuple], name: str) -> "DeviceBatch":
+        """ProjectionExec arithmetic (BinaryExpr Plus / Minus / Multiply over Decimal128, binary.rs:260-275): nodes in post
+        order - ("col", column) | ("lit", unscaled int, precision, scale) | ("add" | "sub" | "mul", left node, right node) -
+        the last node is the root.  Returns this batch plus the root as one more column `name`."""
+        kinds = {"col": 0, "lit": 1, "add": 2, "sub": 3, "mul": 4}
+        arr = (N.ExprNode * max(1, len(nodes)))()
+        sch = self.schema
+        for i, nd in enumerate(nodes):
+            arr[i].kind = kinds[nd[0]]
+            if nd[0] == "col":
+                arr[i].column = _col_index(sch, nd[1])
+            elif nd[0] == "lit":
+                v = nd[1] & ((1 << 128) - 1)
+                arr[i].lit_lo, arr[i].lit_hi = v & ((1 << 64) - 1), v >> 64
+                arr[i].lit_precision, arr[i].lit_scale = nd[2], nd[3]
+            else:
+                arr[i].left, arr[i].right = nd[1], nd[2]
+        h = C.c_void_p()
+        N.check(N.lib().dfgpu_batch_eval_decimal(self.ctx.h, self.h, arr, len(nodes), name.encode(), C.byref(h)))
+        return DeviceBatch(self.ctx, h, keep=self)
+
     def filter(self, predicate: Union[int, str]) -> "DeviceBatch":
         """FilterExec::batch_filter (filter.rs:315-327): rows where the Boolean column `predicate` is true and not NULL."""
         h = C.c_void_p()

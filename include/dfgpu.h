@@ -148,6 +148,25 @@ dfgpu_status dfgpu_coalescer_push(dfgpu_coalescer *c, const struct ArrowArray *b
 dfgpu_status dfgpu_coalescer_finish(dfgpu_coalescer *c, dfgpu_batch **out);
 void dfgpu_coalescer_destroy(dfgpu_coalescer *c);
 
+/* ProjectionExec arithmetic: BinaryExpr {Plus, Minus, Multiply} over Decimal128 columns and literals,
+ * physical-expr/src/expressions/binary.rs:260-275 -> arrow-rs add_wrapping / sub_wrapping / mul_wrapping, which for
+ * decimals derive the result type (+/-: scale max(s1,s2), precision min(38, scale + max(p1-s1, p2-s2) + 1);
+ * *: precision min(38, p1+p2+1), scale s1+s2) and compute checked in i128 on the valid slots (NULL if either side is).
+ * nodes[] is the expression in post order (children before parents, the last node is the root); the planner's casts
+ * are already applied (an Int64 literal arrives as Decimal128(20,0)).  The result batch holds the input columns
+ * (shared, not copied) plus the root as one more Decimal128 column called `name`.
+ * Execution("Arrow error: Compute error: Overflow ...") when an intermediate leaves i128. */
+enum { DFGPU_EXPR_COLUMN = 0, DFGPU_EXPR_LITERAL = 1, DFGPU_EXPR_ADD = 2, DFGPU_EXPR_SUB = 3, DFGPU_EXPR_MUL = 4 };
+typedef struct dfgpu_expr_node {
+    int32_t kind;                 /* DFGPU_EXPR_*                                      */
+    int32_t column;               /* COLUMN: column of the batch (Decimal128)          */
+    int32_t left, right;          /* ADD / SUB / MUL: indices of earlier nodes         */
+    uint64_t lit_lo, lit_hi;      /* LITERAL: unscaled value, two's complement         */
+    int32_t lit_precision, lit_scale;
+} dfgpu_expr_node;
+dfgpu_status dfgpu_batch_eval_decimal(dfgpu_ctx *ctx, const dfgpu_batch *batch, const dfgpu_expr_node *nodes,
+                                      int32_t n_nodes, const char *name, dfgpu_batch **out);
+
 /* FilterExec: `batch_filter` -> arrow `filter_record_batch` (physical-plan/src/filter.rs:315-327).
  * predicate_col is the Boolean column the predicate PhysicalExpr evaluated to; the output holds every column of the
  * input (project afterwards) restricted to the rows where the predicate is true and not NULL, in input order. */

@@ -266,6 +266,73 @@ def filter_batch(batch: pa.RecordBatch, predicate: int) -> pa.RecordBatch:
     return pa.record_batch([c.take(idx) for c in batch.columns], schema=batch.schema)
 
 
+# Decimal128 arithmetic of ProjectionExec: BinaryExpr::evaluate (physical-expr/src/expressions/binary.rs:260-275) calls
+# arrow-rs `add_wrapping` / `sub_wrapping` / `mul_wrapping` (arrow-arith 50, numeric.rs `decimal_op`; un-vendored).  For
+# decimals those kernels derive the result type and compute CHECKED on the valid slots:
+#   + / - : scale = max(s1, s2); precision = min(38, scale + max(p1 - s1, p2 - s2) + 1);
+#           l * 10^(scale - s1) +/- r * 10^(scale - s2), every step checked in i128
+#   *     : precision = min(38, p1 + p2 + 1); scale = s1 + s2 (error if > 38); l * r checked in i128
+# Pinned by decimal.slt:229-360 (c1+1, c1+c5, c1-1, c1-c5, c1*20, c1*c5: types and values).
+I128_MAX = (1 << 127) - 1
+I128_MIN = -(1 << 127)
+
+
+def decimal_result_type(op: str, lt: pa.DataType, rt: pa.DataType) -> pa.DataType:
+    p1, s1, p2, s2 = lt.precision, lt.scale, rt.precision, rt.scale
+    if op in ("add", "sub"):
+        s = max(s1, s2)
+        return pa.decimal128(min(38, s + max(p1 - s1, p2 - s2) + 1), s)
+    if op == "mul":
+        if s1 + s2 > 38:
+            raise OracleError(f"Invalid argument error: Output scale of {lt} * {rt} would exceed max scale of 38")
+        return pa.decimal128(min(38, p1 + p2 + 1), s1 + s2)
+    raise OracleError(op)
+
+
+def _chk(v: int, what: str) -> int:
+    if v > I128_MAX or v < I128_MIN:
+        raise OracleError(f"Arrow error: Compute error: Overflow happened on: {what}")
+    return v
+
+
+def eval_decimal(batch: pa.RecordBatch, nodes: Sequence[tuple]) -> pa.Array:
+    """nodes (post-order, the last one is the root): ("col", index) | ("lit", unscaled int, precision, scale) |
+    ("add" | "sub" | "mul", left node, right node).  Returns the Decimal128 array of the root."""
+    n = batch.num_rows
+    vals, types = [], []
+    for nd in nodes:
+        if nd[0] == "col":
+            c = batch.column(nd[1])
+            if not pa.types.is_decimal128(c.type):
+                raise OracleError(f"NotImplemented: decimal arithmetic over {c.type}")
+            s = c.type.scale
+            vals.append([None if v is None else int(v.scaleb(s)) for v in c.to_pylist()])
+            types.append(c.type)
+        elif nd[0] == "lit":
+            vals.append([nd[1]] * n)
+            types.append(pa.decimal128(nd[2], nd[3]))
+        else:
+            op, li, ri = nd
+            lt, rt = types[li], types[ri]
+            t = decimal_result_type(op, lt, rt)
+            out = []
+            for a, b in zip(vals[li], vals[ri]):
+                if a is None or b is None:
+                    out.append(None)
+                elif op == "mul":
+                    out.append(_chk(a * b, f"{a} * {b}"))
+                else:
+                    la = _chk(a * 10 ** (t.scale - lt.scale), f"{a} * 10^{t.scale - lt.scale}")
+                    rb = _chk(b * 10 ** (t.scale - rt.scale), f"{b} * 10^{t.scale - rt.scale}")
+                    out.append(_chk(la + rb if op == "add" else la - rb, f"{la} {'+' if op == 'add' else '-'} {rb}"))
+            vals.append(out)
+            types.append(t)
+    import decimal as _d
+    ctx = _d.Context(prec=60)
+    t = types[-1]
+    return pa.array([None if v is None else ctx.create_decimal(v).scaleb(-t.scale, ctx) for v in vals[-1]], t)
+
+
 def partition(batch: pa.RecordBatch, key_idx: Sequence[int], n_parts: int) -> List[Optional[pa.RecordBatch]]:
     """BatchPartitioner::partition (repartition/mod.rs:133-217): empty partitions are not produced."""
     ids = partition_ids([batch.column(i) for i in key_idx], n_parts)

@@ -228,6 +228,15 @@ def agg_cases():
     d["count_by_c1"], d["count_by_c1_src"] = after("select count(*),c1 from decimal_simple group by c1 order by c1;")
     d["count_by_c1_c4"], d["count_by_c1_c4_src"] = after(
         "select count(*),c1,c4 from decimal_simple group by c1,c4 order by c1,c4;")
+    d["c5"] = [r["c5"] for r in rows]
+    d["c5_type"] = [12, 7]
+    arith = {}
+    for name, q in [("c1+1", "c1+1"), ("c1+c5", "c1+c5"), ("c1-1", "c1-1"), ("c1-c5", "c1-c5"), ("c1*20", "c1*20"), ("c1*c5", "c1*c5")]:
+        typ, src1 = after("select arrow_typeof(%s) from decimal_simple limit 1;" % q)
+        valsq, src2 = after("select %s from decimal_simple;" % q)
+        m = re.match(r"Decimal128\((\d+),", typ[0][0])
+        arith[name] = {"type": [int(m.group(1)), int(typ[0][1].rstrip(")"))], "values_rowsort": [v[0] for v in valsq], "source": src1 + " / " + src2}
+    d["arithmetic"] = arith
     out["decimal_slt"] = d
     # aggregate.slt: grouped BIT_AND / BIT_OR / BIT_XOR over `bit_aggregate_functions`
     # (the table literal and the `GROUP BY tag` answer; SMALLINT columns, c3 nullable)

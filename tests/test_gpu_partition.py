@@ -170,3 +170,66 @@ def test_coalesce_batches_vs_concat():
     with pytest.raises(Exception, match="not implemented|NotImplemented"):
         df.GpuCoalesceBatchesExec(ctx, pa.schema([("d", pa.dictionary(pa.int32(), pa.string()))]), 100)
     ctx.close()
+
+
+# ---- ProjectionExec arithmetic over Decimal128 (dfgpu_batch_eval_decimal) ----
+def test_decimal_arithmetic_golden_slt():
+    """decimal.slt:205-362: c1+1, c1+c5, c1-1, c1-c5, c1*20, c1*c5 - result types and values."""
+    import datafusion_upstream_b200 as df
+    from test_oracle_golden import AGGS, DEC_ARITH, decimal_simple
+    import decimal
+    ctx = gpu_ctx()
+    dev = df.DeviceBatch.from_arrow(ctx, decimal_simple())
+    for name, nodes in DEC_ARITH.items():
+        g = AGGS["decimal_slt"]["arithmetic"][name]
+        out = dev.eval_decimal(nodes, name).to_arrow()
+        assert out.num_columns == 3 and out.schema.names[2] == name
+        assert out.column(2).type == pa.decimal128(*g["type"])
+        assert sorted(out.column(2).to_pylist()) == sorted(decimal.Decimal(v) for v in g["values_rowsort"])
+    ctx.close()
+
+
+def test_decimal_arithmetic_vs_oracle_q1_projections():
+    """l_extendedprice * (1 - l_discount) and that * (1 + l_tax) (TPC-H Q1's projections) on random Decimal128(15,2) columns
+    with nulls, negative values and slices; bit-exact against the oracle, types Decimal128(38,4) / (38,6)."""
+    import datafusion_upstream_b200 as df
+    import decimal
+    rng = np.random.default_rng(99)
+    ctx = gpu_ctx()
+    n = 50_001
+    d152 = pa.decimal128(15, 2)
+    def col(lo, hi, nulls):
+        return pa.array([decimal.Decimal(int(x)).scaleb(-2) for x in rng.integers(lo, hi, n)], d152, mask=(rng.random(n) < nulls) if nulls else None)
+    b = pa.record_batch([col(-10_000_000, 10_495_001, 0.1), col(0, 11, 0.05), col(0, 9, 0.0), pa.array(rng.integers(0, 9, n), pa.int32())],
+                        names=["price", "disc", "tax", "other"])
+    disc_price = [("col", 0), ("lit", 1, 20, 0), ("col", 1), ("sub", 1, 2), ("mul", 0, 3)]
+    charge = disc_price + [("lit", 1, 20, 0), ("col", 2), ("add", 5, 6), ("mul", 4, 7)]
+    for batch in (b, b.slice(13, 40_000)):
+        dev = df.DeviceBatch.from_arrow(ctx, batch)
+        for nodes, t in ((disc_price, pa.decimal128(38, 4)), (charge, pa.decimal128(38, 6))):
+            got = dev.eval_decimal(nodes, "x").to_arrow()
+            want = oracle.eval_decimal(batch, nodes)
+            assert got.column(4).type == t == want.type
+            assert got.column(4).to_pylist() == want.to_pylist()
+            assert got.column(0).to_pylist() == batch.column(0).to_pylist()       # the input columns ride along untouched
+    ctx.close()
+
+
+def test_decimal_arithmetic_errors():
+    import datafusion_upstream_b200 as df
+    import decimal
+    ctx = gpu_ctx()
+    big = pa.record_batch([pa.array([decimal.Decimal(10) ** 37, None, decimal.Decimal(3)], pa.decimal128(38, 0)),
+                           pa.array([decimal.Decimal("0.1")] * 3, pa.decimal128(38, 20)), pa.array([1, 2, 3], pa.int64())], names=["x", "s", "i"])
+    dev = df.DeviceBatch.from_arrow(ctx, big)
+    with pytest.raises(Exception, match="Overflow"):
+        dev.eval_decimal([("col", 0), ("col", 0), ("mul", 0, 1)], "y")            # 10^74 leaves i128 (arrow: mul_checked)
+    ok = dev.slice(1, 2).eval_decimal([("col", 0), ("col", 0), ("mul", 0, 1)], "y").to_arrow()
+    assert ok.column(3).to_pylist() == [None, decimal.Decimal(9)]                 # NULL slots are not computed
+    with pytest.raises(Exception, match="max scale"):
+        dev.eval_decimal([("col", 1), ("col", 1), ("mul", 0, 1)], "y")
+    with pytest.raises(Exception, match="not implemented|NotImplemented"):
+        dev.eval_decimal([("col", 2), ("col", 0), ("add", 0, 1)], "y")
+    with pytest.raises(Exception, match="post order|precede"):
+        dev.eval_decimal([("col", 0), ("add", 0, 2), ("col", 0)], "y")
+    ctx.close()

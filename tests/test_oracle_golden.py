@@ -231,3 +231,49 @@ def test_bool_and_or_groups_accumulator():
     out = a.emit()
     assert out.schema.field(1).type == pa.bool_()
     assert_rows_equal(rows_of(out), [(1, False, True), (2, False, True), (3, None, None), (4, False, False)])
+
+
+# ---- Decimal128 arithmetic of ProjectionExec, pinned by decimal.slt:205-362 ----
+DEC_ARITH = {
+    "c1+1": [("col", 0), ("lit", 1, 20, 0), ("add", 0, 1)],        # the planner casts the Int64 literal to Decimal128(20, 0)
+    "c1+c5": [("col", 0), ("col", 1), ("add", 0, 1)],
+    "c1-1": [("col", 0), ("lit", 1, 20, 0), ("sub", 0, 1)],
+    "c1-c5": [("col", 0), ("col", 1), ("sub", 0, 1)],
+    "c1*20": [("col", 0), ("lit", 20, 20, 0), ("mul", 0, 1)],
+    "c1*c5": [("col", 0), ("col", 1), ("mul", 0, 1)],
+}
+
+
+def decimal_simple():
+    d = AGGS["decimal_slt"]
+    c1 = pa.array([decimal.Decimal(v) for v in d["c1"]], pa.decimal128(*d["c1_type"]))
+    c5 = pa.array([decimal.Decimal(v) for v in d["c5"]], pa.decimal128(*d["c5_type"]))
+    return pa.record_batch([c1, c5], names=["c1", "c5"])
+
+
+@pytest.mark.parametrize("name", list(DEC_ARITH))
+def test_decimal_arithmetic_slt(name):
+    g = AGGS["decimal_slt"]["arithmetic"][name]
+    out = oracle.eval_decimal(decimal_simple(), DEC_ARITH[name])
+    assert out.type == pa.decimal128(*g["type"])
+    assert sorted(out.to_pylist()) == sorted(decimal.Decimal(v) for v in g["values_rowsort"])
+
+
+def test_decimal_arithmetic_q1_types_nulls_overflow():
+    # Q1's projections: price * (1 - discount) -> Decimal128(38, 4); that * (1 + tax) -> Decimal128(38, 6)  
+    d152 = pa.decimal128(15, 2)
+    b = pa.record_batch([pa.array([decimal.Decimal("100.00"), None, decimal.Decimal("-7.25")], d152),
+                         pa.array([decimal.Decimal("0.05"), decimal.Decimal("0.01"), None], d152),
+                         pa.array([decimal.Decimal("0.08")] * 3, d152)], names=["price", "disc", "tax"])
+    disc_price = [("col", 0), ("lit", 1, 20, 0), ("col", 1), ("sub", 1, 2), ("mul", 0, 3)]
+    out = oracle.eval_decimal(b, disc_price)
+    assert out.type == pa.decimal128(38, 4) and out.to_pylist() == [decimal.Decimal("95.0000"), None, None]
+    charge = disc_price + [("lit", 1, 20, 0), ("col", 2), ("add", 5, 6), ("mul", 4, 7)]
+    out = oracle.eval_decimal(b, charge)
+    assert out.type == pa.decimal128(38, 6) and out.to_pylist() == [decimal.Decimal("102.600000"), None, None]
+    big = pa.record_batch([pa.array([decimal.Decimal(10) ** 37], pa.decimal128(38, 0))], names=["x"])
+    with pytest.raises(oracle.OracleError, match="Overflow"):
+        oracle.eval_decimal(big, [("col", 0), ("col", 0), ("mul", 0, 1)])
+    with pytest.raises(oracle.OracleError, match="max scale"):
+        oracle.eval_decimal(pa.record_batch([pa.array([decimal.Decimal("0.1")], pa.decimal128(38, 20))], names=["x"]),
+                            [("col", 0), ("col", 0), ("mul", 0, 1)])
