@@ -263,6 +263,24 @@ def build_workload(args, df, ctx, torch, device, rank):
                       A(df.AggFunc.Avg, "l_discount", "avg_disc"), A(df.AggFunc.Count, None, "count_order")]
         w["in_bytes"] = (90 if args.q1_keys == "utf8" else 82) * n
         w["out_row_bytes"] = 0
+        if args.q1_project:
+            # disc_price = l_extendedprice * (1 - l_discount) and charge = disc_price * (1 + l_tax) are computed on
+            # the device (dfgpu_batch_eval_decimal) instead of arriving as columns: 4 Decimal128 inputs (66 B/row) instead of 5
+            g2 = torch.Generator(device=device)
+            g2.manual_seed(4242 + rank)
+            tv = torch.randint(0, 9, (n,), generator=g2, device=device, dtype=torch.int64)
+            cols["tax"] = torch.stack([tv, tv >> 63], dim=1).contiguous()
+            order = ["qty", "price", "disc", "tax"]
+            w["host_schema"] = pa.schema(list(schema)[:5] + [pa.field("l_tax", d152)])
+            bufs = bufs[:2] + [{"buffers": [None, cols[c].data_ptr()]} for c in order]
+            w["dev"] = df.DeviceBatch.from_device(ctx, w["host_schema"], bufs, n, keep=(flag, status, cols, keep_offs))
+            schema = pa.schema(list(w["host_schema"]) + [pa.field("disc_price", d384), pa.field("charge", d386)])
+            w["schema"] = schema
+            disc_price = [("col", 3), ("lit", 1, 20, 0), ("col", 4), ("sub", 1, 2), ("mul", 0, 3)]      # price * (1 - disc)
+            charge = [("col", 6), ("lit", 1, 20, 0), ("col", 5), ("add", 1, 2), ("mul", 0, 3)]          # disc_price * (1 + tax)
+            w["prepare"] = lambda d: d.eval_decimal(disc_price, "disc_price").eval_decimal(charge, "charge")
+            w["in_bytes"] -= 16 * n
+            w["name"] += " + projections disc_price / charge evaluated on the device (66 B/row in)"
         kcols = [("l_returnflag", pa.string(), (offs, flag)), ("l_linestatus", pa.string(), (offs, status))] if args.q1_keys == "utf8" else \
                 [("l_returnflag", pa.uint8(), flag), ("l_linestatus", pa.uint8(), status)]
         host_cols = kcols + \
@@ -380,6 +398,8 @@ def run_ours(args):
     def step(inp, to_host=False):
         """One pass of the hot path over one batch.  inp: DeviceBatch (inputs resident in HBM) or a pinned
         host RecordBatch (H2D inside the step); to_host: read the result back into host Arrow buffers."""
+        if w.get("prepare"):
+            inp = w["prepare"](inp if isinstance(inp, df.DeviceBatch) else df.DeviceBatch.from_arrow(ctx, inp))
         if world == 1:
             op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
             op.push(inp)
@@ -449,7 +469,7 @@ def run_ours(args):
     # ---- e2e: host (pinned) Arrow buffers through the C-ABI, H2D + D2H inside the timed region ----
     e2e = None
     if not args.no_e2e:
-        hb, keep, h2d = pinned_batch(ctx, w["schema"], w["host_cols"], n, torch)
+        hb, keep, h2d = pinned_batch(ctx, w.get("host_schema", w["schema"]), w["host_cols"], n, torch)
         e2e_steps = max(1, min(args.steps, 5))
         exported = []
         if args.batch_rows > 0 and world == 1:
@@ -964,6 +984,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--batch-rows", type=int, default=0, help="e2e leg: push the host batch in slices of this many rows (8192 = the reference's batch_size)")
     ap.add_argument("--q1-keys", default="u8", choices=["u8", "utf8"], help="q1: key columns as 2 x UInt8 (default) or 2 x Utf8 as in configs[0]")
+    ap.add_argument("--q1-project", action="store_true", help="q1: compute disc_price / charge on the device from price, discount, tax")
     ap.add_argument("--chunk-rows", type=int, default=0, help="dfgpu_options.chunk_rows (rows per internal launch wave; 0 = default)")
     ap.add_argument("--coalesce-rows", type=int, default=0, help="dfgpu_options.coalesce_rows (0 = default 1 Mi, -1 = off)")
     ap.add_argument("--no-cpu", action="store_true")

@@ -1340,8 +1340,13 @@ DF_D bool mul128_checked(__int128 a, __int128 b, __int128 &r) {
     const unsigned __int128 ua = a < 0 ? (unsigned __int128)(-(a + 1)) + 1 : (unsigned __int128)a;
     const unsigned __int128 ub = b < 0 ? (unsigned __int128)(-(b + 1)) + 1 : (unsigned __int128)b;
     const unsigned __int128 lim = neg ? ((unsigned __int128)1 << 127) : (((unsigned __int128)1 << 127) - 1);
-    if (ua > lim / ub) return false;
-    const unsigned __int128 m = ua * ub;
+    unsigned __int128 m;
+    if (((uint64_t)(ua >> 63) | (uint64_t)(ub >> 63)) == 0) {
+        m = (unsigned __int128)(uint64_t)ua * (uint64_t)ub;  // both magnitudes below 2^63: the product is below 2^126 (the common case; no division)
+    } else {
+        if (ua > lim / ub) return false;
+        m = ua * ub;
+    }
     r = neg ? (__int128)(~m + 1) : (__int128)m;
     return true;
 }
