@@ -62,3 +62,31 @@ def test_schema_roundtrip_without_gpu(lib):
     s = N.export_schema(pa.schema([("a", pa.int64()), ("d", pa.decimal128(15, 2)), ("s", pa.dictionary(pa.int32(), pa.string()))]))
     assert s.format == b"+s" and s.n_children == 3
     N.release_schema(s)
+
+
+def test_struct_layouts_match_the_header(tmp_path):
+    """include/dfgpu.h compiles as plain C (what cgo / bindgen / cffi would consume) and the ctypes mirrors of its structs
+    have the same size and field offsets - an appended dfgpu_options field that the binding misses would otherwise pass
+    silently (the library reads past the caller's struct)."""
+    from datafusion_upstream_b200 import _native as N
+    structs = {"dfgpu_options": N.Options, "dfgpu_agg_desc": N.AggDesc, "dfgpu_metrics": N.Metrics, "dfgpu_expr_node": N.ExprNode,
+               "struct ArrowArray": N.ArrowArray, "struct ArrowSchema": N.ArrowSchema}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "dfgpu.h"', 'int main(void) {']
+    for cname, ct in structs.items():
+        lines.append(f'  printf("{cname} size %zu\\n", sizeof({cname}));')
+        for fname, _ in ct._fields_:
+            lines.append(f'  printf("{cname} {fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ["  return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = str(tmp_path / "layout")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", exe], check=True)
+    out = subprocess.run([exe], capture_output=True, text=True, check=True).stdout
+    got = {}
+    for ln in out.strip().splitlines():
+        name, field, v = ln.rsplit(" ", 2)
+        got[(name, field)] = int(v)
+    for cname, ct in structs.items():
+        assert got[(cname, "size")] == C.sizeof(ct), cname
+        for fname, _ in ct._fields_:
+            assert got[(cname, fname)] == getattr(ct, fname).offset, (cname, fname)
