@@ -929,6 +929,11 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if args.workload not in ("c2", "q1"):
+        # the headline workload (c2) and q1 have a partition-parallel oracle driver; the other workloads report their CPU
+        # baseline inside their own bench line (cpu_baseline)
+        print(json.dumps({"impl": "reference", "unavailable": f"reference arm covers --workload c2 and q1, not {args.workload}"}))
+        return
     import oracle
     threads = os.cpu_count() or 1
     n = min(args.rows, args.cpu_sample)
