@@ -234,6 +234,15 @@ def build_workload(args, df, ctx, torch, device, rank):
         w["out_row_bytes"] = 16
         host_cols = [("UserID", pa.int64(), keys)]
         w["cpu"] = lambda threads, sample: oracle.bench_groupby_count_i64(keys[:sample].cpu().numpy(), threads)
+
+        def acero(sample):
+            t = pa.table({"UserID": keys[:sample].cpu().numpy()})
+            t0 = time.perf_counter()
+            r = t.group_by("UserID").aggregate([([], "count_all")])
+            dt = time.perf_counter() - t0
+            return {"value": sample / dt, "unit": "rows/s", "cores": pa.cpu_count(), "groups": r.num_rows,
+                    "sample": f"first {sample} rows, pyarrow {pa.__version__} Table.group_by(UserID).aggregate(count_all)"}
+        w["acero"] = acero
     elif args.workload == "q1":
         flag, status, cols = gen_q1(n, 42 + rank, device)
         d152, d384, d386 = pa.decimal128(15, 2), pa.decimal128(38, 4), pa.decimal128(38, 6)
@@ -548,6 +557,12 @@ def run_ours(args):
         shape = "P=%d Partial -> hash repartition -> FinalPartitioned" % threads if threads > 1 else "one Single-mode operator (scalar port)"
         cpu = {"value": sample / secs, "unit": "rows/s", "cores": threads, "kind": "port",
                "sample": f"first {sample} rows of the same workload, {shape}, 8192-row batches"}
+        if w.get("acero"):
+            # a second, independent CPU data point: pyarrow's Acero hash aggregation on the same Arrow columns
+            try:
+                cpu["acero"] = w["acero"](min(n, 20_000_000))
+            except Exception as e:      # the bench line must not depend on it
+                cpu["acero"] = {"unavailable": str(e)[:120]}
     if rank == 0:
         line = {
             "metric": "input rows/s (hash aggregation, device-resident input) and HBM GB/s", "value": value, "unit": "rows/s",
