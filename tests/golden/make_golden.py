@@ -279,6 +279,56 @@ def agg_cases():
                       "input": items, "expected": None if exp.group(1) is None else int(exp.group(1)),
                       "source": "datafusion/physical-expr/src/aggregate/bit_and_or_xor.rs:%d" % (n + 1)})
     out["bit_unit_tests"] = units
+    # sum.rs / average.rs / count.rs / min_max.rs unit tests of the simple shape
+    #   let a: ArrayRef = Arc::new(<T>Array::from(vec![...]));  +  assert_aggregate(a, AggregateFunction::F, false, EXPECTED)
+    #                                                           or generic_test_op!(a, DataType::T, Op, EXPECTED)
+    # (known answers of SUM / AVG / COUNT / MIN / MAX incl. null handling and result types)
+    ARR = {"Int32Array": "int32", "UInt32Array": "uint32", "Int64Array": "int64", "Float32Array": "float32", "Float64Array": "float64"}
+    def scalar(txt):
+        m = re.match(r"ScalarValue::from\(([-0-9._]+?)_?(i32|i64|u32|u64|f32|f64)\)", txt)
+        if m:
+            t = {"i32": "int32", "i64": "int64", "u32": "uint32", "u64": "uint64", "f32": "float32", "f64": "float64"}[m.group(2)]
+            v = m.group(1).replace("_", "")
+            return (float(v) if t.startswith("float") else int(float(v))), t
+        m = re.match(r"ScalarValue::(Int32|Int64|UInt32|UInt64|Float32|Float64)\(None\)", txt)
+        if m:
+            return None, m.group(1).lower()
+        return "skip", None
+    simple = []
+    for rel in ("sum.rs", "average.rs", "count.rs", "min_max.rs"):
+        src = read("datafusion/physical-expr/src/aggregate/" + rel)
+        for n, l in enumerate(src):
+            m = re.match(r"\s*fn (\w+)\(\)", l)
+            if not m:
+                continue
+            body = " ".join(x.strip() for x in src[n + 1:n + 16])
+            end = body.find(" fn ")
+            body = body if end < 0 else body[:end]
+            am = re.search(r"Arc::new\((\w+Array)::from\(vec!\[(.*?)\]\)\)", body)
+            fm = re.search(r"assert_aggregate\(\s*a,\s*AggregateFunction::(\w+),\s*false,\s*(ScalarValue::[^;]*?)\s*\);", body) or \
+                 re.search(r"generic_test_op!\(\s*a,\s*DataType::\w+,\s*(\w+),\s*(ScalarValue::\w+\([^()]*(?:\([^()]*\))?\))", body)
+            if not am or not fm or am.group(1) not in ARR or body.count("generic_test_op!") + body.count("assert_aggregate(") != 1:
+                continue
+            vals = []
+            okv = True
+            for t in am.group(2).split(","):
+                t = t.strip()
+                if not t:
+                    continue
+                if t == "None":
+                    vals.append(None)
+                    continue
+                mm = re.match(r"(?:Some\()?(-?[0-9.]+)(?:_?(?:i32|u32|i64|f32|f64))?\)?$", t.replace("_u32", "").replace("_f32", "").replace("_f64", ""))
+                if not mm:
+                    okv = False
+                    break
+                vals.append(float(mm.group(1)) if "Float" in am.group(1) else int(float(mm.group(1))))
+            exp, et = scalar(fm.group(2))
+            if not okv or exp == "skip":
+                continue
+            simple.append({"name": m.group(1), "func": fm.group(1).lower(), "input_type": ARR[am.group(1)], "input": vals,
+                           "expected": exp, "expected_type": et, "source": "datafusion/physical-expr/src/aggregate/%s:%d" % (rel, n + 1)})
+    out["simple_unit_tests"] = simple
     return out
 
 

@@ -357,3 +357,18 @@ def test_host_batch_coalescing(keys, target):
     assert op.metrics()["input_batches"] == len(pieces) and op.metrics()["input_rows"] == whole.num_rows
     op.close()
     ctx.close()
+
+
+PA_T = {"int32": pa.int32(), "uint32": pa.uint32(), "int64": pa.int64(), "uint64": pa.uint64(), "float32": pa.float32(),
+        "float64": pa.float64()}
+
+
+@pytest.mark.parametrize("case", AGGS["simple_unit_tests"], ids=[c["name"] for c in AGGS["simple_unit_tests"]])
+def test_golden_simple_unit_vectors(ctx, case):
+    """sum.rs:359-400, average.rs:631-673, count.rs:343-361, min_max.rs:1285-1406: known answers incl. all-NULL inputs."""
+    t = PA_T[case["input_type"]]
+    v = pa.array(case["input"], t)
+    b = pa.record_batch([pa.array([0] * len(v), pa.int8()), v], names=["k", "v"])
+    out = gpu_agg(ctx, "single", [b], ["k"], [(case["func"], "v", "r", None)])
+    assert out.schema.field(1).type == PA_T[case["expected_type"]], case["source"]
+    assert out.column(1).to_pylist() == [case["expected"]], case["source"]

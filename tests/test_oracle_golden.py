@@ -277,3 +277,19 @@ def test_decimal_arithmetic_q1_types_nulls_overflow():
     with pytest.raises(oracle.OracleError, match="max scale"):
         oracle.eval_decimal(pa.record_batch([pa.array([decimal.Decimal("0.1")], pa.decimal128(38, 20))], names=["x"]),
                             [("col", 0), ("col", 0), ("mul", 0, 1)])
+
+
+# ---- sum.rs / average.rs / count.rs / min_max.rs unit-test known answers (values, NULL handling, result types) ----
+PA_T = {"int32": pa.int32(), "uint32": pa.uint32(), "int64": pa.int64(), "uint64": pa.uint64(), "float32": pa.float32(),
+        "float64": pa.float64()}
+
+
+@pytest.mark.parametrize("case", AGGS["simple_unit_tests"], ids=[c["name"] for c in AGGS["simple_unit_tests"]])
+def test_simple_unit_vectors(case):
+    t = PA_T[case["input_type"]]
+    v = pa.array(case["input"], t)
+    a = OracleAgg("single", ["k"], [pa.int8()], [AggSpec(case["func"], "r", t)])
+    a.push([pa.array([0] * len(v), pa.int8())], [v])
+    out = a.emit()
+    assert out.schema.field(1).type == PA_T[case["expected_type"]], case["source"]
+    assert out.column(1).to_pylist() == [case["expected"]], case["source"]
