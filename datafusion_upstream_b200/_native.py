@@ -85,6 +85,7 @@ SYMBOLS = [
     "dfgpu_join_metrics", "dfgpu_join_destroy", "dfgpu_partition_hash", "dfgpu_exchange_all_to_all",
     "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter", "dfgpu_batch_eval_decimal",
     "dfgpu_coalescer_create", "dfgpu_coalescer_push", "dfgpu_coalescer_finish", "dfgpu_coalescer_destroy",
+    "dfgpu_partition_i64_noalloc",
 ]
 
 _lib = None
@@ -155,6 +156,7 @@ def lib():
     L.dfgpu_exchange_all_to_all.argtypes = [P, C.POINTER(P), P, C.POINTER(P)]
     L.dfgpu_exchange_all_gather.argtypes = [P, P, P, C.POINTER(P)]
     L.dfgpu_nccl_get_unique_id.argtypes = [P]
+    L.dfgpu_partition_i64_noalloc.argtypes = [P, P, P, C.c_int64, C.c_int32, P, P]
     _lib = L
     return L
 

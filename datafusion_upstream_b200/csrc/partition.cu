@@ -7,6 +7,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <mutex>
 
 #include "device.cuh"
 #include "groups.h"
@@ -566,6 +567,109 @@ Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) 
     return out.release();
 }
 
+
+// ---- allocation-free partitioning (dfgpu_partition_i64_noalloc) ---------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it): the scratch partition_perm() takes from the stream-ordered pool (partition ids, per-block histogram,
+// scanned write positions) lives in ONE file-scope device array instead.  Every GPU that loads the library holds
+// these ~5 MiB until exit.  All calls on a device share the array and it keeps the last call's contents: the
+// ticket is cleared at the start of every call, everything else is fully rewritten before it is read.  Calls that
+// overlap on the GPU (different streams, different host threads) race on it.
+static const int NA_ROWS_PER_BLOCK = 4096;
+static const int NA_MAX_BLOCKS = DFGPU_NOALLOC_MAX_ROWS / NA_ROWS_PER_BLOCK;
+struct NaScratch {
+    unsigned int ticket;  // blocks of k_na_count that have published their histogram column; must start at 0
+    unsigned int pad[63];
+    uint32_t pid[DFGPU_NOALLOC_MAX_ROWS];                              // partition of every row
+    int64_t hist[(size_t)DFGPU_NOALLOC_MAX_PARTS * NA_MAX_BLOCKS];     // [P][nblocks] rows per partition and block
+    int64_t starts[(size_t)DFGPU_NOALLOC_MAX_PARTS * NA_MAX_BLOCKS];   // exclusive scan of hist
+};
+static __device__ __align__(256) NaScratch g_na_scratch;
+
+// pass 1 of partition_perm() (k_part_count) with the hash computed in place, plus the scan: the block that
+// publishes the last histogram column scans all of them (at most 65 536 counters) and writes the partition offsets.
+__global__ void __launch_bounds__(PART_T) k_na_count(const int64_t *__restrict__ keys, const uint8_t *__restrict__ validity, int64_t n,
+                                                     int64_t rows_per_block, int P, NaScratch *__restrict__ sc,
+                                                     int64_t *__restrict__ offsets_out) {
+    __shared__ uint32_t cnt[DFGPU_NOALLOC_MAX_PARTS];
+    __shared__ int64_t tsum[PART_T];
+    __shared__ bool last;
+    for (int p = threadIdx.x; p < P; p += PART_T) cnt[p] = 0;
+    __syncthreads();
+    const int64_t lo = (int64_t)blockIdx.x * rows_per_block, hi = min(n, lo + rows_per_block);
+    for (int64_t i = lo + threadIdx.x; i < hi; i += PART_T) {
+        // create_hashes over one Int64 column, seeds (0,0,0,0): a NULL row keeps the initial hash 0 (hash_utils.rs:117-131)
+        const uint64_t h = (validity && !bit_get(validity, i)) ? 0 : h_u64((uint64_t)keys[i], 0);
+        const uint32_t p = (uint32_t)(h % (uint64_t)P);  // repartition/mod.rs:184-187
+        sc->pid[i] = p;
+        atomicAdd(&cnt[p], 1u);
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < P; p += PART_T) sc->hist[(int64_t)p * gridDim.x + blockIdx.x] = cnt[p];
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(&sc->ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    const int64_t hn = (int64_t)P * gridDim.x, per = (hn + PART_T - 1) / PART_T;
+    const int64_t a = min(hn, (int64_t)threadIdx.x * per), b = min(hn, a + per);
+    int64_t s = 0;
+    for (int64_t k = a; k < b; k++) s += __ldcg(&sc->hist[k]);
+    tsum[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t run = 0;
+        for (int t = 0; t < PART_T; t++) { const int64_t v = tsum[t]; tsum[t] = run; run += v; }
+    }
+    __syncthreads();
+    int64_t run = tsum[threadIdx.x];
+    for (int64_t k = a; k < b; k++) {
+        sc->starts[k] = run;
+        if (k % gridDim.x == 0) offsets_out[k / gridDim.x] = run;  // partition p starts at starts[p][0]
+        run += __ldcg(&sc->hist[k]);
+    }
+    if (threadIdx.x == 0) offsets_out[P] = n;
+}
+
+// the scratch array's device address, resolved once per device (the symbol's name is only a host-side stand-in)
+static NaScratch *na_scratch_ptr() {
+    static std::mutex mu;
+    static NaScratch *ptrs[64] = {};
+    int dev = 0;
+    DF_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) fail(DFGPU_NOT_IMPLEMENTED, "dfgpu_partition_i64_noalloc: device ordinal above 63");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        NaScratch *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_na_scratch);
+        if (e != cudaSuccess || !p)
+            fail(DFGPU_CUDA, std::string("dfgpu_partition_i64_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+        ptrs[dev] = p;
+    }
+    return ptrs[dev];
+}
+
+static void partition_i64_noalloc(cudaStream_t st, const int64_t *keys, const uint8_t *validity, int64_t n, int P, int64_t *perm_out,
+                                  int64_t *offsets_out) {
+    if (P <= 0 || P > DFGPU_NOALLOC_MAX_PARTS || n < 0 || n > DFGPU_NOALLOC_MAX_ROWS)
+        fail(DFGPU_NOT_IMPLEMENTED, "dfgpu_partition_i64_noalloc: " + std::to_string(n) + " rows into " + std::to_string(P) +
+                                        " partitions exceeds the static scratch (at most " + std::to_string(DFGPU_NOALLOC_MAX_ROWS) +
+                                        " rows and " + std::to_string(DFGPU_NOALLOC_MAX_PARTS) + " partitions per call); use dfgpu_partition_hash");
+    if (!offsets_out || (n > 0 && (!keys || !perm_out))) fail(DFGPU_INTERNAL, "dfgpu_partition_i64_noalloc: null pointer");
+    if (n == 0) {
+        DF_CUDA(cudaMemsetAsync(offsets_out, 0, (size_t)(P + 1) * 8, st));
+        return;
+    }
+    NaScratch *sc = na_scratch_ptr();
+    DF_CUDA(cudaMemsetAsync(&sc->ticket, 0, sizeof(unsigned int), st));  // the one field that must start at zero
+    const int nblocks = (int)((n + NA_ROWS_PER_BLOCK - 1) / NA_ROWS_PER_BLOCK);
+    k_na_count<<<nblocks, PART_T, 0, st>>>(keys, validity, n, NA_ROWS_PER_BLOCK, P, sc, offsets_out);
+    const size_t smem = (size_t)P * 8 + (size_t)(PART_T / 32) * P * 4;  // <= 10 KiB at P = 256
+    k_part_scatter<<<nblocks, PART_T, smem, st>>>(sc->pid, n, NA_ROWS_PER_BLOCK, P, sc->starts, perm_out);
+    DF_CUDA(cudaGetLastError());
+}
+
 }  // namespace dfgpu
 
 using namespace dfgpu;
@@ -602,6 +706,13 @@ dfgpu_status dfgpu_exchange_all_gather(dfgpu_ctx *ctx, const dfgpu_batch *local,
         // all-gather == all-to-all where every destination receives the same local batch
         std::vector<dfgpu_batch *> parts((size_t)std::max(1, W), const_cast<dfgpu_batch *>(local));
         *out = exchange_all_to_all(ctx, parts.data(), s);
+    } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; }
+    return DFGPU_OK;
+}
+dfgpu_status dfgpu_partition_i64_noalloc(void *stream, const int64_t *dev_keys, const uint8_t *dev_validity, int64_t n, int32_t n_parts,
+                                         int64_t *dev_perm_out, int64_t *dev_offsets_out) {
+    try {
+        partition_i64_noalloc((cudaStream_t)stream, dev_keys, dev_validity, n, n_parts, dev_perm_out, dev_offsets_out);
     } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; }
     return DFGPU_OK;
 }

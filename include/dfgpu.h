@@ -246,6 +246,25 @@ dfgpu_status dfgpu_partition_hash(dfgpu_ctx *ctx, const dfgpu_batch *batch, cons
  * of this rank's parts are NULL). */
 dfgpu_status dfgpu_exchange_all_to_all(dfgpu_ctx *ctx, dfgpu_batch *const *parts, const struct ArrowSchema *schema,
                                        dfgpu_batch **out);
+/* Allocation-free partitioning.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It is the partitioning step of dfgpu_partition_hash for ONE Int64 key column given as raw device pointers
+ * (dev_validity: Arrow validity bitmap of the keys with bit offset 0, or NULL when there are no NULL keys): on
+ * return dev_perm_out[n] holds the row numbers grouped by partition = hash % n_parts, input order kept inside a
+ * partition, and dev_offsets_out[n_parts + 1] the start of every partition in it (the rows of partition p are
+ * dev_perm_out[offsets[p] .. offsets[p + 1])) - the same rows in the same order as dfgpu_partition_hash's out_parts.
+ * The scratch memory (partition ids, per-block histograms, scanned write positions; ~5 MiB) is a file-scope device
+ * array that every GPU that loads the library holds until exit; the call itself performs no cudaMalloc / cudaFree /
+ * pool allocation.  Limits: n <= DFGPU_NOALLOC_MAX_ROWS and n_parts <= DFGPU_NOALLOC_MAX_PARTS per call, otherwise
+ * DFGPU_NOT_IMPLEMENTED (split the batch, or use dfgpu_partition_hash).  The work is enqueued on `stream`
+ * (a cudaStream_t of the calling thread's current device; NULL = the default stream) and NOT synchronised: outputs
+ * are valid once the stream reaches that point.  All calls on a device share the one scratch array: calls that
+ * overlap on the GPU (two streams, two host threads) race - serialise them on one stream.  The first call on a
+ * device resolves the array's device address (cudaGetSymbolAddress); make it outside a graph capture. */
+#define DFGPU_NOALLOC_MAX_ROWS (1 << 20)
+#define DFGPU_NOALLOC_MAX_PARTS 256
+dfgpu_status dfgpu_partition_i64_noalloc(void *stream, const int64_t *dev_keys, const uint8_t *dev_validity, int64_t n,
+                                         int32_t n_parts, int64_t *dev_perm_out, int64_t *dev_offsets_out);
 /* 128-byte ncclUniqueId for dfgpu_options.nccl_unique_id: rank 0 creates it and shares it with
  * the other ranks out of band (the reference has no analogue: its exchange is in-process). */
 dfgpu_status dfgpu_nccl_get_unique_id(void *out128);
