@@ -107,10 +107,25 @@ class FastAgg {
     // finalize() + re-insert the groups as partial-state records; returns the exact group count.
     int64_t compact();
     size_t device_bytes() const;
+    // what the sample of the first push said (tests, metrics): 1 cache path, 2 partition path, 0 not decided yet
+    int path_mode() const { return mode_; }
 
   private:
     void ensure_capacity(int64_t more);
     void reinsert(const FaResult &r);
+    // partition path (fastagg_part.inc): COUNT(*)-shaped operators whose keys no per-CTA cache can hold
+    bool part_eligible(const FaPlan &plan) const;
+    void decide_mode(const FaPlan &plan, int64_t n);
+    void push_part(const FaPlan &plan, int64_t n, int64_t algo_bytes);
+    FaResult finalize_part();
+    void reset_store();
+    struct Piece { BufRef keys, offs, hist; int64_t rows = 0; };
+    std::vector<Piece> pieces_;
+    BufRef hot_keys_, hot_cnt_;
+    int mode_ = 0;               // 0 undecided, 1 cache path (level 1), 2 partition path
+    int64_t sample_distinct_ = -1, sample_rows_ = 0, sample_hot_ = 0;
+    int part_force_ = -1;        // DFGPU_FA_PART: 1 always (when eligible), 0 never, -1 by sample
+    int64_t reserve_hint_ = 0;
     Ctx *ctx_;
     std::vector<FaOpSpec> ops_;
     int SW_ = 0, RW_ = 0, seen_word_ = -1, nbits_ = 0;
