@@ -85,7 +85,7 @@ SYMBOLS = [
     "dfgpu_join_metrics", "dfgpu_join_destroy", "dfgpu_partition_hash", "dfgpu_exchange_all_to_all",
     "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter", "dfgpu_batch_eval_decimal",
     "dfgpu_coalescer_create", "dfgpu_coalescer_push", "dfgpu_coalescer_finish", "dfgpu_coalescer_destroy",
-    "dfgpu_partition_i64_noalloc",
+    "dfgpu_partition_i64_noalloc", "dfgpu_agg_exchange_virtual",
 ]
 
 _lib = None
@@ -124,6 +124,7 @@ def lib():
     L.dfgpu_batch_concat.argtypes = [P, C.POINTER(P), C.c_int32, C.POINTER(P)]
     L.dfgpu_batch_slice.argtypes = [P, P, C.c_int64, C.c_int64, C.POINTER(P)]
     L.dfgpu_agg_exchange.argtypes = [P]
+    L.dfgpu_agg_exchange_virtual.argtypes = [C.POINTER(P), C.c_int32]
     L.dfgpu_batch_project.argtypes = [P, P, C.POINTER(C.c_int32), C.c_int32, C.POINTER(P)]
     L.dfgpu_batch_filter.argtypes = [P, P, C.c_int32, C.POINTER(P)]
     L.dfgpu_batch_eval_decimal.argtypes = [P, P, C.POINTER(ExprNode), C.c_int32, C.c_char_p, C.POINTER(P)]

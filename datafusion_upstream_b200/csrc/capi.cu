@@ -18,6 +18,7 @@ Ctx *agg_ctx(const dfgpu_agg &a);
 void agg_metrics(const dfgpu_agg &a, dfgpu_metrics *out);
 int64_t agg_num_groups(dfgpu_agg &a);
 void agg_exchange(dfgpu_agg &a);
+void agg_exchange_virtual(dfgpu_agg *const *aggs, int n);
 void agg_destroy(dfgpu_agg *a);
 void ctx_init_nccl(Ctx *ctx);
 void ctx_destroy_nccl(Ctx *ctx);
@@ -367,6 +368,13 @@ dfgpu_status dfgpu_agg_exchange(dfgpu_agg *agg) {
     DF_TRY
     DF_CUDA(cudaSetDevice(agg_ctx(*agg)->device));
     agg_exchange(*agg);
+    DF_CATCH
+}
+dfgpu_status dfgpu_agg_exchange_virtual(dfgpu_agg *const *aggs, int32_t n) {
+    DF_TRY
+    if (n < 1 || !aggs) fail(DFGPU_PLAN, "virtual record exchange: no operators");
+    DF_CUDA(cudaSetDevice(agg_ctx(*aggs[0])->device));
+    agg_exchange_virtual(aggs, n);
     DF_CATCH
 }
 dfgpu_status dfgpu_agg_emit(dfgpu_agg *agg, dfgpu_batch **out) {

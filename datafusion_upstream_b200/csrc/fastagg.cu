@@ -419,3 +419,4 @@ __global__ void __launch_bounds__(FA_T1, 2) k_fa_l1(const FaPlan *__restrict__ p
 #include "fastagg_l2.inc"
 #include "fastagg_part.inc"
 #include "fastagg_host.inc"
+#include "fastagg_xchg.inc"

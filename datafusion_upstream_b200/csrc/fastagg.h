@@ -104,6 +104,9 @@ class FastAgg {
     // Partial -> RepartitionExec(Hash) -> FinalPartitioned (physical_planner.rs:814-849) fused at the
     // level of partial-state records: no local final merge, no emit / re-ingest of state batches.
     void exchange();
+    // The same exchange between N operators of ONE process and context ("virtual ranks", SURVEY 8e: how the reference tests
+    // its 4-way partitioned plans in one process, hash_join.rs:1505-1550): ranks[r] plays rank r of a world of ranks.size().
+    static void exchange_virtual(const std::vector<FastAgg *> &ranks);
     // finalize() + re-insert the groups as partial-state records; returns the exact group count.
     int64_t compact();
     size_t device_bytes() const;
@@ -120,6 +123,18 @@ class FastAgg {
     FaResult finalize_part();
     void reset_store();
     struct Piece { BufRef keys, offs, hist; int64_t rows = 0; };
+    // record exchange in phases, so that real ranks (collectives between the phases) and virtual ranks (loops) share them
+    struct Xchg;
+    bool count_only() const { return ops_.size() == 1 && ops_[0].kind == 1 /* OP_COUNT */ && nbits_ == 0 && SW_ == 1; }
+    size_t xchg_meta_bytes() const;
+    void xchg_prepare(Xchg &x, int W, int me);                                      // local: partition order, meta block on the device
+    size_t xchg_plan(Xchg &x, const std::vector<uint8_t> &meta_all);                // from everybody's meta: what goes where; bytes my window needs
+    void xchg_push(Xchg &x, void *const *windows);                                  // my runs -> the owners' windows
+    void xchg_finish(Xchg &x, void *my_window, bool window_borrowed, const BufRef &meta_all_dev);  // pieces of what arrived; side groups
+    std::vector<BufRef> xhold_;        // received window (virtual ranks), gathered meta, piece tables: alive until the merge ran
+    BufRef xp_offs_, xp_hist_;         // [npieces][FA_P] of the received pieces (count-only operators)
+    std::vector<const uint64_t *> xp_base_;
+    std::vector<int> xp_stride_;
     std::vector<Piece> pieces_;
     BufRef hot_keys_, hot_cnt_;
     int mode_ = 0;               // 0 undecided, 1 cache path (level 1), 2 partition path
@@ -137,6 +152,7 @@ class FastAgg {
     BufRef xrecs_, xseg_off_, xseg_cnt_;
     int64_t xR_ = -1;
     int xfirst_ = 0, xcount_ = 0;  // owned partitions [xfirst_, xfirst_ + xcount_)
+    int xW_ = 1;                   // ranks of the exchange that ran
     int64_t cap_ = 0, used_ub_ = 0;
     bool reg_mode_allowed_ = true;
     int reg_stages_ = 4;

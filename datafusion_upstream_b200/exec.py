@@ -341,6 +341,13 @@ class GpuAggregateExec:
         operator cannot exchange at the record level (the caller keeps the three-operator plan)."""
         N.check(N.lib().dfgpu_agg_exchange(self.h))
 
+    @staticmethod
+    def exchange_virtual(ops: Sequence["GpuAggregateExec"]):
+        """The same exchange between operators of one process, ops[r] playing rank r (dfgpu_agg_exchange_virtual): the
+        reference's way of testing partitioned plans in one process (hash_join.rs:1505-1550)."""
+        arr = (C.c_void_p * len(ops))(*[o.h for o in ops])
+        N.check(N.lib().dfgpu_agg_exchange_virtual(arr, len(ops)))
+
     def num_groups(self) -> int:
         n = C.c_int64()
         N.check(N.lib().dfgpu_agg_num_groups(self.h, C.byref(n)))

@@ -208,6 +208,12 @@ dfgpu_status dfgpu_agg_num_groups(dfgpu_agg *agg, int64_t *out);
  * world == 1: no-op.  DFGPU_NOT_IMPLEMENTED (before any communication, identically on every rank) when the
  * operator does not run the two-level path; the caller then keeps the three-operator plan. */
 dfgpu_status dfgpu_agg_exchange(dfgpu_agg *agg);
+/* The same exchange between n operators of ONE process and context, aggs[r] playing rank r of a world of n ("virtual
+ * ranks": how the reference runs its 4-way partitioned plans inside one process, joins/hash_join.rs:1505-1550 and the
+ * target_partitions of core/tests/fuzz_cases/aggregate_fuzz.rs).  The runs move with device-to-device copies instead
+ * of NVLink stores; everything else - partition order, offsets, piece tables, the merge of the owned partitions - is
+ * the code dfgpu_agg_exchange runs.  Afterwards emit every operator: the union of the outputs is the result. */
+dfgpu_status dfgpu_agg_exchange_virtual(dfgpu_agg *const *aggs, int32_t n);
 /* emit(EmitTo::All) (row_hash.rs:626-662); resets the operator like the reference's
  * early emit (row_hash.rs:723-734) so it can be called mid-stream in Partial mode. */
 dfgpu_status dfgpu_agg_emit(dfgpu_agg *agg, dfgpu_batch **out);

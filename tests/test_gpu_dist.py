@@ -88,16 +88,17 @@ def _worker(rank, world, port, n_rows, out_q):
         dist.destroy_process_group()
 
 
-@pytest.mark.timeout(600)
-def test_two_gpu_sharded_aggregate_and_join():
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_multi_gpu_sharded_aggregate_and_join(world):
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run with gpurun --gpus {world}); the same exchange runs between virtual ranks in test_gpu_virtual_ranks.py")
     import torch.multiprocessing as mp
     import oracle
     from gpu_helpers import oracle_agg
     from util import assert_rows_equal, rows_of
-    world, n_rows = 2, 200_003
+    n_rows = 200_003
     mpc = mp.get_context("spawn")
     q = mpc.Queue()
     port = _free_port()
@@ -130,3 +131,78 @@ def test_two_gpu_sharded_aggregate_and_join():
     oj = oracle.hash_join("inner", left.to_batches(), right.to_batches(), [("a", "b")])
     assert sum(r[1] for r in res) == oj.num_rows
     assert sum(r[2] for r in res) == int(np.sum(oj.column(1).to_numpy().astype(np.int64) * 31 + oj.column(3).to_numpy()))
+
+
+def _big_keys(rank, n):
+    """Zipf(1.0) ranks over a shared universe, spread over 64 bits: every rank sees the hot keys, the tail is mostly its own."""
+    rng = np.random.default_rng(1000 + rank)
+    r = np.exp(rng.random(n) * np.log(40_000_000)).astype(np.int64)
+    with np.errstate(over="ignore"):
+        return (r.astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15)).view(np.int64)
+
+
+def _worker_big(rank, world, port, n_rows, s2max, out_q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    if s2max:
+        os.environ["DFGPU_FA_S2MAX"] = s2max
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import datafusion_upstream_b200 as df
+        from datafusion_upstream_b200.dist import bootstrap_nccl_id
+        uid = bootstrap_nccl_id(dist, df.GpuContext.nccl_unique_id)
+        ctx = df.GpuContext(device=rank, rank=rank, world=world, nccl_unique_id=uid)
+        k = _big_keys(rank, n_rows)
+        b = pa.record_batch([pa.array(k, pa.int64())], names=["k"])
+        res = []
+        for specs in ([("count", None, "c")], [("count", None, "c"), ("sum", "k", "s")]):   # partition path (key pieces) / cache path (records)
+            op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, b.schema, ["k"], [df.AggregateExpr(df.AggFunc[f.capitalize()], a, nm) for f, a, nm in specs])
+            op.push(b)
+            op.exchange()
+            out = op.emit()
+            op.close()
+            gk, gc = out.column(0).to_numpy(), out.column(1).to_numpy()
+            with np.errstate(over="ignore"):
+                cks = int((gk.view(np.uint64) * np.uint64(0xBF58476D1CE4E5B9) * gc.astype(np.uint64)).sum(dtype=np.uint64))
+            res.append((len(gk), int(gc.sum()), cks, len(gk) - len(np.unique(gk))))
+        allr = [None] * world
+        dist.all_gather_object(allr, res)
+        if rank == 0:
+            out_q.put(allr)
+        ctx.synchronize()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(1500)
+@pytest.mark.parametrize("s2max", [None, "256"], ids=["default", "tiny_level2_tables"])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_multi_gpu_count_star_20m_rows_per_rank(world, s2max):
+    """20 M rows per rank, ~10 M distinct keys per rank from one universe: groups, sum of counts and a key-weighted checksum of the
+    union against numpy on the same keys; no key may come out twice (tiny level-2 tables force the overflow rounds that once let a
+    key through two rounds at N = 8)."""
+    import torch
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run with gpurun --gpus {world})")
+    import torch.multiprocessing as mp
+    n_rows = 20_000_000
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_worker_big, args=(r, world, port, n_rows, s2max, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=1200)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    allk = np.concatenate([_big_keys(r, n_rows) for r in range(world)])
+    uk, uc = np.unique(allk, return_counts=True)
+    with np.errstate(over="ignore"):
+        want_cks = int((uk.view(np.uint64) * np.uint64(0xBF58476D1CE4E5B9) * uc.astype(np.uint64)).sum(dtype=np.uint64))
+    for variant in range(2):
+        G = sum(r[variant][0] for r in res)
+        rows = sum(r[variant][1] for r in res)
+        cks = sum(r[variant][2] for r in res) % (1 << 64)
+        dup = sum(r[variant][3] for r in res)
+        assert (G, rows, cks, dup) == (len(uk), n_rows * world, want_cks, 0), (variant, G, len(uk), rows, dup)
