@@ -56,6 +56,13 @@ DF_D uint64_t h_bytes(const uint8_t *p, int64_t len, uint64_t seed) {
     if (i < len) h = mix64(h ^ load_le(p + i, (int)(len - i)));
     return h;
 }
+// String ids inside packed key images (groups.h: kind 2 fields).  A string of <= 3 bytes IS its id - the length and the
+// bytes themselves, top bit set - so it needs no table (the inline rule of ArrowBytesMap, physical-expr/src/binary_map.rs:
+// 381-393, at the width of a 4-byte field); longer strings get dense ids < 2^31 from the column's interner.
+static const uint32_t STRID_INLINE = 0x80000000u;
+static const int STRID_INLINE_MAX = 3;
+DF_D uint32_t strid_inline(const uint8_t *p, int len) { return STRID_INLINE | ((uint32_t)len << 24) | (len ? (uint32_t)load_le(p, len) : 0u); }
+
 // a[0, len) == b[0, len), eight bytes per step; CG: b is read through L2
 template <bool CG = false> DF_D bool bytes_equal(const uint8_t *a, const uint8_t *b, int64_t len) {
     int64_t k = 0;

@@ -57,7 +57,7 @@ DF_D void fa_load_key(const FaPlan &pl, int64_t row, uint64_t &key, int &side) {
         if (!col_valid(c, row)) { key = 0; side = 0; return; }
         key = ((const uint64_t *)c.values)[row];
     } else {
-        key = 0;
+        key = pl.key_or;
         for (int k = 0; k < pl.nkeys; k++) {
             const FaKeyCol &kc = pl.keys[k];
             if (kc.null_bit >= 0 && !col_valid(kc.v, row)) {
@@ -65,7 +65,12 @@ DF_D void fa_load_key(const FaPlan &pl, int64_t row, uint64_t &key, int &side) {
                 continue;
             }
             uint64_t v;  // raw little-endian bytes of the value, zero-extended
-            if (kc.kind == 1) v = bit_get((const uint8_t *)kc.v.values, kc.v.dbit + row) ? 1 : 0;
+            if (kc.kind == 3) {  // short string: its id is the string itself (NULL is STRID_NULL in the field)
+                const uint8_t *p; int64_t len;
+                if (!col_valid(kc.v, row)) v = STRID_NULL;
+                else { col_bytes(kc.v, row, p, len); v = strid_inline(p, (int)len); }
+            }
+            else if (kc.kind == 1) v = bit_get((const uint8_t *)kc.v.values, kc.v.dbit + row) ? 1 : 0;
             else if (kc.w == 1) v = ((const uint8_t *)kc.v.values)[row];
             else if (kc.w == 2) v = ((const uint16_t *)kc.v.values)[row];
             else if (kc.w == 4) v = ((const uint32_t *)kc.v.values)[row];

@@ -28,7 +28,7 @@ static const uint64_t FA_EMPTY = ~0ULL;    // free-slot marker; the real key ~0 
 
 struct FaKeyCol {
     ColView v;
-    int32_t kind, off, w, null_bit;  // kind 0: fixed width, 1: bool
+    int32_t kind, off, w, null_bit;  // kind 0: fixed width, 1: bool, 3: Utf8 / Binary of <= 3 bytes read in place (inline string id)
 };
 struct FaOp {
     ColView val, filt;
@@ -42,6 +42,7 @@ struct FaPlan {
     FaOp ops[FA_MAX_OPS];
     int32_t nkeys, direct, null_off, nops;
     int32_t SW, RW, seen_word, pad;  // state words / record words (1 + SW) / index of the seen word or -1
+    uint64_t key_or;                 // constant bits of the image (the tag and length of constant-length inline strings)
 };
 
 // register mode of level 1 (fastagg_reg.inc)

@@ -97,6 +97,8 @@ class GroupTable {
     // per-row ids of the Utf8/Binary key column `c` of a packed layout (interned in that column's own table;
     // STRID_NULL for NULL): lets the two-level path treat the column as a 4-byte field of the key image
     BufRef string_field_ids(size_t c, const DevCol &col, int64_t row_off, int64_t n) { return string_ids(cols_[c], col, row_off, n, false); }
+    // shortest / longest value and first offset of rows [row_off, row_off + n) of a Utf8 / Binary key column -> dev_out3[0..2]
+    void string_field_lengths(const DevCol &col, int64_t row_off, int64_t n, unsigned long long *dev_out3);
     void adopt_dense(const BufRef &keys, int64_t null_gid) {
         gkeys_ = keys;
         tv_.gkeys = keys ? keys->as<uint64_t>() : nullptr;
