@@ -86,6 +86,7 @@ SYMBOLS = [
     "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter", "dfgpu_batch_eval_decimal",
     "dfgpu_coalescer_create", "dfgpu_coalescer_push", "dfgpu_coalescer_finish", "dfgpu_coalescer_destroy",
     "dfgpu_partition_i64_noalloc", "dfgpu_agg_exchange_virtual",
+    "dfgpu_join_set_filter", "dfgpu_join_probe_candidates", "dfgpu_join_probe_commit",
 ]
 
 _lib = None
@@ -151,6 +152,9 @@ def lib():
     L.dfgpu_join_build_finish.argtypes = [P]
     L.dfgpu_join_probe.argtypes = [P, P, C.POINTER(P)]
     L.dfgpu_join_emit_unmatched.argtypes = [P, C.POINTER(P)]
+    L.dfgpu_join_set_filter.argtypes = [P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32]
+    L.dfgpu_join_probe_candidates.argtypes = [P, P, C.POINTER(P)]
+    L.dfgpu_join_probe_commit.argtypes = [P, P, C.c_int32, C.POINTER(P)]
     L.dfgpu_join_metrics.argtypes = [P, C.POINTER(Metrics)]
     L.dfgpu_join_destroy.argtypes = [P]
     L.dfgpu_partition_hash.argtypes = [P, P, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.POINTER(P)]

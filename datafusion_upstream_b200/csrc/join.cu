@@ -31,6 +31,16 @@ struct dfgpu_join {
     bool fast = false;
     int64_t build_rows = 0, num_keys = 0;
     bool finished = false;
+    // residual JoinFilter (joins/utils.rs:1143-1176): the columns of the intermediate batch, and the candidate pairs of the
+    // probe batch whose predicate the host is evaluating (between probe_candidates and probe_commit)
+    bool has_filter = false;
+    std::vector<std::pair<int, int>> filter_cols;  // (side: 0 build / 1 probe, column)
+    struct Pending {
+        bool valid = false;
+        dfgpu::BufRef ob, op;
+        int64_t total = 0, np = 0;
+        std::vector<dfgpu::ColRef> probe_cols;
+    } pend;
     dfgpu_metrics m;
 };
 
@@ -281,7 +291,7 @@ static void build_index(JoinOp &j) {
 }
 
 // fused probe: returns the (build_idx, probe_idx) pairs and their number
-static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op) {
+static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op, int jt_use, bool mark_visited) {
     Ctx *ctx = j.ctx;
     cudaStream_t st = ctx->stream;
     const int64_t np = probe.num_rows;
@@ -296,10 +306,10 @@ static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRe
     {
         KTimer kt(ctx, "k_jp_count", np * 8);
         if (jk.direct)
-            k_jp_count<true><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
+            k_jp_count<true><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, jt_use, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
                                                             tot->as<unsigned long long>(), sup->as<unsigned long long>());
         else
-            k_jp_count<false><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, j.join_type, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
+            k_jp_count<false><<<(unsigned)nt, JP_T, 0, st>>>(jk, ix, np, jt_use, lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(),
                                                              tot->as<unsigned long long>(), sup->as<unsigned long long>());
     }
     // the output size = sum of the super-tile sums (a few KB): summed on the host
@@ -313,9 +323,9 @@ static int64_t probe_pairs_fast(JoinOp &j, const Batch &probe, BufRef &ob, BufRe
     {
         KTimer kt(ctx, "k_jp_emit", total * 28);
         k_jp_emit<<<(unsigned)nt, JE_T, 0, st>>>(lsp->as<uint64_t>(), lrow->as<uint16_t>(), tne->as<uint32_t>(), tot->as<unsigned long long>(),
-                                                 sup->as<unsigned long long>(), j.join_type,
+                                                 sup->as<unsigned long long>(), jt_use,
                                                  j.rows->as<uint32_t>(), ob->as<int64_t>(), op->as<int64_t>(),
-                                                 j.visited ? j.visited->as<uint8_t>() : nullptr);
+                                                 (mark_visited && j.visited) ? j.visited->as<uint8_t>() : nullptr);
     }
     note_launch(ctx, 2);
     DF_CUDA(cudaGetLastError());
@@ -383,11 +393,11 @@ static Batch *empty_output(JoinOp &j) {
 }
 
 // general probe: intern the probe keys against the GroupTable (any key shape), then count -> scan -> scatter
-static int64_t probe_pairs_general(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op) {
+static int64_t probe_pairs_general(JoinOp &j, const Batch &probe, BufRef &ob, BufRef &op, int jt_use, bool mark_visited) {
     Ctx *ctx = j.ctx;
     cudaStream_t st = ctx->stream;
     const int64_t np = probe.num_rows;
-    const int jt = j.join_type;
+    const int jt = jt_use;
     BufRef gids = make_buf(ctx, (size_t)np * 4 + 16);
     int grid = grid_for(np, 256, ctx, 32);
     bool have_table = j.build_rows > 0 && j.num_keys > 0;
@@ -412,7 +422,7 @@ static int64_t probe_pairs_general(JoinOp &j, const Batch &probe, BufRef &ob, Bu
     }
     ob = make_buf(ctx, (size_t)total * 8 + 16);
     op = make_buf(ctx, (size_t)total * 8 + 16);
-    uint8_t *visited = j.visited ? j.visited->as<uint8_t>() : nullptr;
+    uint8_t *visited = (mark_visited && j.visited) ? j.visited->as<uint8_t>() : nullptr;
     {
         KTimer kt(ctx, "k_probe_scatter", np * 12 + total * 16);
         k_probe_scatter<<<grid, 256, 0, st>>>(gids->as<uint32_t>(), np, span, have_table ? j.rows->as<uint32_t>() : nullptr, offs->as<int64_t>(),
@@ -422,58 +432,202 @@ static int64_t probe_pairs_general(JoinOp &j, const Batch &probe, BufRef &ob, Bu
     return total;
 }
 
+// build_batch_from_indices (joins/utils.rs:1180-1230): the output columns of `total` (build_idx, probe_idx) pairs, -1 = NULL side
+static Batch *materialize(JoinOp &j, const std::vector<ColRef> &probe_cols, const BufRef &ob, const BufRef &op, int64_t total) {
+    Ctx *ctx = j.ctx;
+    const int jt = j.join_type;
+    const bool left_out = jt != DFGPU_JOIN_RIGHT_SEMI && jt != DFGPU_JOIN_RIGHT_ANTI;
+    const bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
+    if (!right_out) return empty_output(j);  // LeftSemi / LeftAnti emit nothing per probe batch (utils.rs:1269-1277)
+    std::unique_ptr<Batch> out(new Batch());
+    out->ctx = ctx;
+    out->num_rows = total;
+    size_t fi = 0;
+    const bool build_nullable = jt == DFGPU_JOIN_RIGHT || jt == DFGPU_JOIN_FULL;
+    if (left_out && j.build_rows == 0)
+        for (auto &c : j.build->cols) {
+            ColRef t = col_nulls(ctx, c->type, total);
+            t->type = j.out_schema.fields[fi++];
+            out->cols.push_back(t);
+        }
+    std::vector<const DevCol *> srcs;
+    std::vector<const int64_t *> idx;
+    std::vector<bool> may_null;
+    if (left_out && j.build_rows != 0)
+        for (auto &c : j.build->cols) {
+            srcs.push_back(c.get());
+            idx.push_back(ob->as<int64_t>());
+            may_null.push_back(build_nullable);
+        }
+    for (auto &c : probe_cols) {
+        srcs.push_back(c.get());
+        idx.push_back(op->as<int64_t>());
+        may_null.push_back(false);
+    }
+    for (auto &t : cols_take(ctx, srcs, idx, total, may_null)) {
+        t->type = j.out_schema.fields[fi++];
+        out->cols.push_back(t);
+    }
+    return out.release();
+}
+
 Batch *join_probe(JoinOp &j, const Batch &probe) {
     Ctx *ctx = j.ctx;
-    cudaStream_t st = ctx->stream;
     auto t0 = std::chrono::steady_clock::now();
     if (!j.finished) fail(DFGPU_INTERNAL, "probe before build_finish");
+    if (j.has_filter) fail(DFGPU_INTERNAL, "this join has a residual JoinFilter: use dfgpu_join_probe_candidates / dfgpu_join_probe_commit");
     if (probe.cols.size() != j.probe_schema.fields.size()) fail(DFGPU_INTERNAL, "probe batch does not match the probe schema");
     int64_t np = probe.num_rows;
     j.m.input_batches += 1;
     j.m.input_rows += np;
-    int jt = j.join_type;
     if (np == 0) return empty_output(j);
-    bool left_out = jt != DFGPU_JOIN_RIGHT_SEMI && jt != DFGPU_JOIN_RIGHT_ANTI;
-    bool right_out = jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI;
     BufRef ob, op;
     int64_t total = 0;
-    if (j.fast) total = probe_pairs_fast(j, probe, ob, op);
-    else total = probe_pairs_general(j, probe, ob, op);
+    if (j.fast) total = probe_pairs_fast(j, probe, ob, op, j.join_type, true);
+    else total = probe_pairs_general(j, probe, ob, op, j.join_type, true);
     KTimer kt_gather(ctx, "probe_gather(col_take)", total * 16);
     DF_CUDA(cudaGetLastError());
+    std::unique_ptr<Batch> out(materialize(j, probe.cols, ob, op, total));
+    j.m.output_batches += 1;
+    j.m.output_rows += out->num_rows;
+    j.m.join_time_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+    return out.release();
+}
+
+// ---- residual JoinFilter ------------------------------------------------------------------------------------
+// The reference applies the filter to the candidate pairs BEFORE it marks build rows visited and before the join-type
+// fix-ups (hash_join.rs:1259-1311), so the predicate decides which rows count as matched.  PhysicalExpr::evaluate stays in
+// the host engine, hence two calls: probe_candidates returns the intermediate batch of the filter's columns for every
+// equi-join candidate pair (build_batch_from_indices over filter.column_indices, utils.rs:1154-1162), the host evaluates
+// the predicate on it, and probe_commit takes the Boolean result and finishes the probe batch.
+__global__ void k_mark_u8(const int64_t *__restrict__ idx, int64_t n, uint8_t *__restrict__ flags) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) flags[idx[i]] = 1;
+}
+__global__ void k_fill_i64(int64_t *p, int64_t v, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+void join_set_filter(JoinOp &j, const int32_t *sides, const int32_t *cols, int n) {
+    if (j.finished || !j.pending.empty()) fail(DFGPU_INTERNAL, "set_filter after the build side was pushed");
+    j.filter_cols.clear();
+    for (int i = 0; i < n; i++) {
+        const auto &sch = sides[i] == 0 ? j.build_schema : j.probe_schema;
+        if ((sides[i] != 0 && sides[i] != 1) || cols[i] < 0 || cols[i] >= (int)sch.fields.size()) fail(DFGPU_PLAN, "JoinFilter column index out of range");
+        j.filter_cols.push_back({sides[i], cols[i]});
+    }
+    j.has_filter = true;
+}
+
+Batch *join_probe_candidates(JoinOp &j, const Batch &probe) {
+    Ctx *ctx = j.ctx;
+    if (!j.finished) fail(DFGPU_INTERNAL, "probe before build_finish");
+    if (!j.has_filter) fail(DFGPU_INTERNAL, "probe_candidates: the join has no JoinFilter (use dfgpu_join_probe)");
+    if (j.pend.valid) fail(DFGPU_INTERNAL, "probe_candidates: the previous probe batch was not committed");
+    if (probe.cols.size() != j.probe_schema.fields.size()) fail(DFGPU_INTERNAL, "probe batch does not match the probe schema");
+    const int64_t np = probe.num_rows;
+    j.m.input_batches += 1;
+    j.m.input_rows += np;
+    BufRef ob, op;
+    int64_t total = 0;
+    if (np > 0) {   // every equi-join match, nothing marked yet: the Inner pairs
+        if (j.fast) total = probe_pairs_fast(j, probe, ob, op, DFGPU_JOIN_INNER, false);
+        else total = probe_pairs_general(j, probe, ob, op, DFGPU_JOIN_INNER, false);
+    }
+    if (!ob) { ob = make_buf(ctx, 16); op = make_buf(ctx, 16); }
+    j.pend.valid = true;
+    j.pend.ob = ob;
+    j.pend.op = op;
+    j.pend.total = total;
+    j.pend.np = np;
+    j.pend.probe_cols = probe.cols;
     std::unique_ptr<Batch> out(new Batch());
     out->ctx = ctx;
-    if (!right_out) {  // LeftSemi / LeftAnti emit nothing per probe batch (utils.rs:1269-1277)
-        out.reset(empty_output(j));
-    } else {
-        out->num_rows = total;
-        size_t fi = 0;
-        bool build_nullable = jt == DFGPU_JOIN_RIGHT || jt == DFGPU_JOIN_FULL;
-        if (left_out && j.build_rows == 0)
-            for (auto &c : j.build->cols) {
-                ColRef t = col_nulls(ctx, c->type, total);
-                t->type = j.out_schema.fields[fi++];
-                out->cols.push_back(t);
-            }
-        std::vector<const DevCol *> srcs;
-        std::vector<const int64_t *> idx;
-        std::vector<bool> may_null;
-        if (left_out && j.build_rows != 0)
-            for (auto &c : j.build->cols) {
-                srcs.push_back(c.get());
-                idx.push_back(ob->as<int64_t>());
-                may_null.push_back(build_nullable);
-            }
-        for (auto &c : probe.cols) {
-            srcs.push_back(c.get());
-            idx.push_back(op->as<int64_t>());
-            may_null.push_back(false);
-        }
-        for (auto &t : cols_take(ctx, srcs, idx, total, may_null)) {
-            t->type = j.out_schema.fields[fi++];
-            out->cols.push_back(t);
-        }
+    out->num_rows = total;
+    for (auto &fc : j.filter_cols) {
+        const DevCol &src = fc.first == 0 ? *j.build->cols[(size_t)fc.second] : *probe.cols[(size_t)fc.second];
+        if (fc.first == 0 && j.build_rows == 0) { out->cols.push_back(col_nulls(ctx, src.type, 0)); continue; }
+        out->cols.push_back(col_take(ctx, src, fc.first == 0 ? ob->as<int64_t>() : op->as<int64_t>(), total, false));
     }
+    return out.release();
+}
+
+Batch *join_probe_commit(JoinOp &j, const Batch &mask, int mask_col) {
+    Ctx *ctx = j.ctx;
+    cudaStream_t st = ctx->stream;
+    auto t0 = std::chrono::steady_clock::now();
+    if (!j.pend.valid) fail(DFGPU_INTERNAL, "probe_commit without probe_candidates");
+    if (mask_col < 0 || mask_col >= (int)mask.cols.size() || mask.cols[(size_t)mask_col]->type.id != T_BOOL)
+        fail(DFGPU_PLAN, "probe_commit: the filter result must be a Boolean column");   // as_boolean_array (utils.rs:1168)
+    if (mask.num_rows != j.pend.total) fail(DFGPU_INTERNAL, "probe_commit: the filter result has " + std::to_string(mask.num_rows) + " rows for " + std::to_string(j.pend.total) + " candidate pairs");
+    JoinOp::Pending pd = std::move(j.pend);
+    j.pend = JoinOp::Pending();
+    const int jt = j.join_type;
+    // compute::filter of both index arrays by the mask (utils.rs:1170-1171; a NULL predicate counts as false)
+    auto i64col = [&](const BufRef &b, int64_t n) {
+        auto c = std::make_shared<DevCol>();
+        c->type = make_type(T_I64, "i", false);
+        c->length = n;
+        c->values = b->ptr;
+        c->owned.push_back(b);
+        return c;
+    };
+    Batch pairs;
+    pairs.ctx = ctx;
+    pairs.num_rows = pd.total;
+    pairs.cols = {i64col(pd.ob, pd.total), i64col(pd.op, pd.total), mask.cols[(size_t)mask_col]};
+    std::unique_ptr<Batch> kept(batch_filter(ctx, &pairs, 2));
+    const int64_t K = kept->num_rows;
+    const int64_t *fb = (const int64_t *)kept->cols[0]->values, *fp = (const int64_t *)kept->cols[1]->values;
+    if (K && need_final(jt)) {   // mark joined build rows visited (hash_join.rs:1274-1278)
+        k_mark_u8<<<grid_for(K, 256, ctx, 16), 256, 0, st>>>(fb, K, j.visited->as<uint8_t>());
+        note_launch(ctx);
+    }
+    // adjust_indices_by_join_type (utils.rs:1234-1279) over the whole probe batch
+    BufRef ob, op;
+    int64_t total = 0;
+    if (jt == DFGPU_JOIN_INNER || jt == DFGPU_JOIN_LEFT) {
+        ob = K ? make_borrowed(ctx, (void *)fb, (size_t)K * 8) : make_buf(ctx, 16);   // (`kept` outlives the gather below)
+        op = K ? make_borrowed(ctx, (void *)fp, (size_t)K * 8) : make_buf(ctx, 16);
+        total = K;
+    } else if (jt != DFGPU_JOIN_LEFT_SEMI && jt != DFGPU_JOIN_LEFT_ANTI) {
+        const int64_t np = pd.np;
+        BufRef hit = make_buf(ctx, (size_t)np + 16, true);
+        if (K) k_mark_u8<<<grid_for(K, 256, ctx, 16), 256, 0, st>>>(fp, K, hit->as<uint8_t>());
+        // probe rows with (RightSemi) / without (Right, Full, RightAnti) a surviving pair, in row order
+        int64_t U = 0;
+        BufRef uidx = make_buf(ctx, 16);
+        if (np) {
+            BufRef counts = make_buf(ctx, (size_t)np * 8 + 16), offs = make_buf(ctx, (size_t)np * 8 + 16);
+            k_flags_to_counts<<<grid_for(np, 256, ctx, 32), 256, 0, st>>>(hit->as<uint8_t>(), np, jt == DFGPU_JOIN_RIGHT_SEMI ? 1 : 0, counts->as<int64_t>());
+            exclusive_scan_i64(ctx, counts->as<int64_t>(), offs->as<int64_t>(), np, &U);
+            uidx = make_buf(ctx, (size_t)U * 8 + 16);
+            k_compact<<<grid_for(np, 256, ctx, 32), 256, 0, st>>>(counts->as<int64_t>(), offs->as<int64_t>(), np, uidx->as<int64_t>());
+            note_launch(ctx, 3);
+        }
+        if (jt == DFGPU_JOIN_RIGHT || jt == DFGPU_JOIN_FULL) {   // pairs ++ (NULL, unmatched probe row) (utils.rs:1248-1254)
+            total = K + U;
+            ob = make_buf(ctx, (size_t)total * 8 + 16);
+            op = make_buf(ctx, (size_t)total * 8 + 16);
+            if (K) {
+                DF_CUDA(cudaMemcpyAsync(ob->ptr, fb, (size_t)K * 8, cudaMemcpyDeviceToDevice, st));
+                DF_CUDA(cudaMemcpyAsync(op->ptr, fp, (size_t)K * 8, cudaMemcpyDeviceToDevice, st));
+            }
+            if (U) {
+                k_fill_i64<<<grid_for(U, 256, ctx, 16), 256, 0, st>>>(ob->as<int64_t>() + K, -1, U);
+                DF_CUDA(cudaMemcpyAsync(op->as<int64_t>() + K, uidx->ptr, (size_t)U * 8, cudaMemcpyDeviceToDevice, st));
+                note_launch(ctx);
+            }
+        } else {   // RightSemi / RightAnti: probe side only
+            total = U;
+            op = uidx;
+            ob = make_buf(ctx, 16);
+        }
+    } else {
+        ob = make_buf(ctx, 16);
+        op = make_buf(ctx, 16);
+    }
+    DF_CUDA(cudaGetLastError());
+    std::unique_ptr<Batch> out(materialize(j, pd.probe_cols, ob, op, total));
     j.m.output_batches += 1;
     j.m.output_rows += out->num_rows;
     j.m.join_time_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
@@ -557,6 +711,23 @@ dfgpu_status dfgpu_join_probe(dfgpu_join *join, const dfgpu_batch *probe, dfgpu_
     J_TRY
     DF_CUDA(cudaSetDevice(join->ctx->device));
     *out = join_probe(*join, *probe);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_set_filter(dfgpu_join *join, const int32_t *sides, const int32_t *columns, int32_t n) {
+    J_TRY
+    join_set_filter(*join, sides, columns, n);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_probe_candidates(dfgpu_join *join, const dfgpu_batch *probe, dfgpu_batch **out_intermediate) {
+    J_TRY
+    DF_CUDA(cudaSetDevice(join->ctx->device));
+    *out_intermediate = join_probe_candidates(*join, *probe);
+    J_CATCH
+}
+dfgpu_status dfgpu_join_probe_commit(dfgpu_join *join, const dfgpu_batch *filter_result, int32_t column, dfgpu_batch **out) {
+    J_TRY
+    DF_CUDA(cudaSetDevice(join->ctx->device));
+    *out = join_probe_commit(*join, *filter_result, column);
     J_CATCH
 }
 dfgpu_status dfgpu_join_emit_unmatched(dfgpu_join *join, dfgpu_batch **out) {

@@ -407,9 +407,18 @@ class GpuHashJoinExec:
             N.release_schema(ls)
             N.release_schema(rs)
         self.h = h
+        self._predicate = None
         o = N.ArrowSchema()
         N.check(N.lib().dfgpu_join_output_schema(self.h, C.addressof(o)))
         self.schema = N.import_schema(o)
+
+    def set_filter(self, column_indices: Sequence[tuple], predicate):
+        """Residual JoinFilter (joins/utils.rs:1143-1176): column_indices = [(side, column)] with side "left" | "right"; predicate is the
+        host engine's PhysicalExpr: RecordBatch of the intermediate columns -> Boolean array.  Call before build()."""
+        sides = (C.c_int32 * len(column_indices))(*[0 if s == "left" else 1 for s, _ in column_indices])
+        cols = (C.c_int32 * len(column_indices))(*[int(i) for _, i in column_indices])
+        N.check(N.lib().dfgpu_join_set_filter(self.h, sides, cols, len(column_indices)))
+        self._predicate = predicate
 
     def build(self, batches: Iterable[BatchLike]):
         """collect_left_input (hash_join.rs:678-768)."""
@@ -421,6 +430,18 @@ class GpuHashJoinExec:
     def probe_device(self, batch: BatchLike) -> DeviceBatch:
         d = _dev(self.ctx, batch)
         h = C.c_void_p()
+        if getattr(self, "_predicate", None) is not None:
+            # candidate pairs -> intermediate batch -> the host evaluates the predicate -> commit (hash_join.rs:1259-1311)
+            N.check(N.lib().dfgpu_join_probe_candidates(self.h, d.h, C.byref(h)))
+            inter = DeviceBatch(self.ctx, h).to_arrow()
+            mask = self._predicate(inter)
+            mask = pa.array(mask) if not isinstance(mask, (pa.Array, pa.ChunkedArray)) else mask
+            if isinstance(mask, pa.ChunkedArray):
+                mask = mask.combine_chunks() if mask.num_chunks else pa.array([], pa.bool_())
+            md = DeviceBatch.from_arrow(self.ctx, pa.record_batch([mask.cast(pa.bool_())], names=["filter"]))
+            h2 = C.c_void_p()
+            N.check(N.lib().dfgpu_join_probe_commit(self.h, md.h, 0, C.byref(h2)))
+            return DeviceBatch(self.ctx, h2)
         N.check(N.lib().dfgpu_join_probe(self.h, d.h, C.byref(h)))
         return DeviceBatch(self.ctx, h)
 

@@ -235,6 +235,21 @@ dfgpu_status dfgpu_join_build_finish(dfgpu_join *join);
  * the visited bitmap is updated with atomics.  Output holds every row the reference emits
  * for this probe batch (all its <=batch_size sub-batches concatenated). */
 dfgpu_status dfgpu_join_probe(dfgpu_join *join, const dfgpu_batch *probe, dfgpu_batch **out);
+/* Residual JoinFilter (joins/utils.rs:1143-1176; JoinFilter = expression + column_indices + intermediate schema).  The
+ * reference applies it to the candidate pairs of the equi-join BEFORE it marks build rows visited and BEFORE
+ * adjust_indices_by_join_type (hash_join.rs:1259-1311), so for every join type but Inner it decides which rows count as
+ * matched and cannot be applied to the joined output afterwards.  The predicate is a PhysicalExpr and is evaluated by the
+ * host engine, hence three calls:
+ *   set_filter        once, before the build side is pushed: filter.column_indices as (side, column) pairs, side 0 = left
+ *                     / build, 1 = right / probe (JoinSide, common/src/join_type.rs:111-116)
+ *   probe_candidates  instead of dfgpu_join_probe: returns the intermediate batch of those columns, one row per candidate
+ *                     pair (what apply_join_filter_to_indices builds with build_batch_from_indices, utils.rs:1154-1162)
+ *   probe_commit      the Boolean column the predicate evaluated to on that batch (NULL = false, arrow `filter`): filters
+ *                     the pairs, marks visited build rows, applies the join type's fix-ups over the probe batch and returns
+ *                     its output rows.  Exactly one commit per probe_candidates. */
+dfgpu_status dfgpu_join_set_filter(dfgpu_join *join, const int32_t *sides, const int32_t *columns, int32_t n);
+dfgpu_status dfgpu_join_probe_candidates(dfgpu_join *join, const dfgpu_batch *probe, dfgpu_batch **out_intermediate);
+dfgpu_status dfgpu_join_probe_commit(dfgpu_join *join, const dfgpu_batch *filter_result, int32_t column, dfgpu_batch **out);
 /* process_unmatched_build_batch (hash_join.rs:1348-1388); *out = NULL when the join type
  * produces nothing at the end (Inner, Right, RightSemi, RightAnti). */
 dfgpu_status dfgpu_join_emit_unmatched(dfgpu_join *join, dfgpu_batch **out);

@@ -99,6 +99,8 @@ def lib():
         L.oracle_join_probe.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]
         L.oracle_join_unmatched.restype = C.c_int64
         L.oracle_join_unmatched.argtypes = [C.c_void_p]
+        L.oracle_join_set_filter.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oracle_join_set_filter.restype = None
         L.oracle_join_out_build.restype = C.POINTER(C.c_int64)
         L.oracle_join_out_build.argtypes = [C.c_void_p]
         L.oracle_join_out_probe.restype = C.POINTER(C.c_int64)
@@ -493,6 +495,28 @@ class OracleJoin:
         self.build_batches: List[pa.RecordBatch] = []
         self.build_cat: Optional[pa.RecordBatch] = None
         self.out_batches = 0
+        self._filter_cb = None
+        self._probe_batch = None
+
+    def set_filter(self, column_indices: Sequence[tuple], predicate):
+        """JoinFilter (joins/utils.rs:1143-1176): column_indices = [(side, index)] with side "left" | "right" selects the columns of
+        the intermediate batch; predicate(intermediate RecordBatch) -> Boolean array; NULL counts as false (arrow `filter`)."""
+        FN = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_uint8))
+
+        def cb(_user, bi, pi, n, keep):
+            b = np.ctypeslib.as_array(bi, shape=(n,)).copy()
+            p = np.ctypeslib.as_array(pi, shape=(n,)).copy()
+            cols = []
+            for side, idx in column_indices:
+                src, ix = (self.build_cat, b) if side == "left" else (self._probe_batch, p)
+                cols.append(src.column(idx).take(pa.array(ix)))
+            inter = pa.RecordBatch.from_arrays(cols, names=[f"c{i}" for i in range(len(cols))])
+            mask = predicate(inter)
+            m = np.asarray(pa.compute.fill_null(mask, False)) if len(mask) else np.zeros(0, bool)
+            for i in range(n):
+                keep[i] = 1 if m[i] else 0
+        self._filter_cb = FN(cb)
+        lib().oracle_join_set_filter(self.h, self._filter_cb, None)
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -531,6 +555,7 @@ class OracleJoin:
         keep: list = []
         arr = _col_array([batch.column(r) for _, r in self.on], keep)
         nb = C.c_int64(0)
+        self._probe_batch = batch
         n = lib().oracle_join_probe(self.h, arr, C.byref(nb))
         self.out_batches += nb.value
         self.probe_schema = batch.schema
@@ -545,9 +570,12 @@ class OracleJoin:
 
 def hash_join(join_type: str, left: Sequence[pa.RecordBatch], right: Sequence[pa.RecordBatch], on,
               null_equals_null=False, batch_size=8192, force_collisions=False,
-              left_schema=None, right_schema=None) -> pa.Table:
-    """One HashJoinExec partition: collect build, stream probe batches, then unmatched rows."""
+              left_schema=None, right_schema=None, filter=None) -> pa.Table:
+    """One HashJoinExec partition: collect build, stream probe batches, then unmatched rows.
+    filter = (column_indices, predicate): the residual JoinFilter, see OracleJoin.set_filter."""
     j = OracleJoin(join_type, on, null_equals_null, batch_size, force_collisions)
+    if filter is not None:
+        j.set_filter(*filter)
     left_schema = left_schema or left[0].schema
     right_schema = right_schema or right[0].schema
     j.build(left, left_schema)

@@ -922,6 +922,9 @@ struct oracle_join {
     std::vector<uint8_t> visited;
     std::vector<int64_t> out_build, out_probe;
     bool finished = false;
+    // JoinFilter (joins/utils.rs:1143-1176): the driver evaluates the residual predicate on the candidate pairs
+    oracle_join_filter_fn filter = nullptr;
+    void *filter_user = nullptr;
 
     bool locate(int64_t idx, int64_t &b, int64_t &r) const {
         for (size_t k = 0; k < cat_batch.size(); k++) {
@@ -1061,6 +1064,16 @@ extern "C" int64_t oracle_join_probe(oracle_join *j, const ocol *const *key_cols
                 eq = key_equal(j->build_batches[(size_t)b][(size_t)c], r, key_cols[c], pi[k], j->null_equals_null);
             if (eq) { fb.push_back(bi[k]); fp.push_back(pi[k]); }
         }
+        // apply_join_filter_to_indices (hash_join.rs:1259-1271, utils.rs:1143-1176): BEFORE the visited bits and the
+        // join-type fix-ups, so the residual predicate decides which rows count as matched
+        if (j->filter && !fb.empty()) {
+            std::vector<uint8_t> keep(fb.size(), 0);
+            j->filter(j->filter_user, fb.data(), fp.data(), (int64_t)fb.size(), keep.data());
+            size_t w = 0;
+            for (size_t k = 0; k < fb.size(); k++)
+                if (keep[k]) { fb[w] = fb[k]; fp[w] = fp[k]; w++; }
+            fb.resize(w); fp.resize(w);
+        }
         if (need_final(j->join_type))  // :1274-1278
             for (auto x : fb) j->visited[(size_t)x] = 1;
         bool last_has = !fp.empty(); int64_t last_joined = last_has ? fp.back() : 0;
@@ -1104,6 +1117,8 @@ extern "C" int64_t oracle_join_probe(oracle_join *j, const ocol *const *key_cols
     if (out_batch_count) *out_batch_count = nbatches;
     return (int64_t)j->out_probe.size();
 }
+
+extern "C" void oracle_join_set_filter(oracle_join *j, oracle_join_filter_fn fn, void *user) { j->filter = fn; j->filter_user = user; }
 
 extern "C" int64_t oracle_join_unmatched(oracle_join *j) {
     j->out_build.clear(); j->out_probe.clear();

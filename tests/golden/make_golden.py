@@ -66,6 +66,51 @@ def parse_build_tables(text):
     return out
 
 
+def filter_join_cases(lines, helpers):
+    """The join_*_with_filter tests (hash_join.rs:2286-3182): every `let expected = [...]` of a test is one case, with the JoinFilter
+    in force at that point - its column_indices [(side, index)] and its BinaryExpr (column 0 <op> literal | column 1)."""
+    s, e = find_fn(lines, "prepare_join_filter")
+    shared = "\n".join(lines[s:e + 1])
+
+    def parse_filter(text):
+        last = text.rfind("let column_indices")
+        cols_text = text[last:] if last >= 0 else text
+        cols = [[side.lower(), int(ix)] for ix, side in re.findall(r"ColumnIndex\s*\{\s*index:\s*(\d+),\s*side:\s*JoinSide::(\w+)", cols_text)]
+        m = None
+        for m in re.finditer(r"BinaryExpr::new\(\s*Arc::new\(Column::new\(\"\w+\",\s*(\d+)\)\),\s*Operator::(\w+),\s*Arc::new\((Literal::new\(ScalarValue::Int32\(Some\((-?\d+)\)\)\)|Column::new\(\"\w+\",\s*(\d+)\))", text):
+            pass
+        rhs = {"lit": int(m.group(4))} if m.group(4) is not None else {"col": int(m.group(5))}
+        return cols, {"lhs": int(m.group(1)), "op": m.group(2), "rhs": rhs}
+    out = []
+    for name in ("join_left_semi_with_filter", "join_right_semi_with_filter", "join_left_anti_with_filter", "join_right_anti_with_filter",
+                 "join_inner_with_filter", "join_left_with_filter", "join_right_with_filter", "join_full_with_filter"):
+        s, e = find_fn(lines, name)
+        body = "\n".join(lines[s:e + 1])
+        tables = parse_build_tables(body)
+        sides = {}
+        for side in ("left", "right"):
+            m = re.search(r"let %s = (build_\w+)\(" % side, body)
+            sides[side] = helpers[m.group(1)] if m.group(1) in helpers else tables.pop(0)
+        on = re.findall(r'Column::new_with_schema\("(\w+)", &(left|right)\.schema\(\)', body)
+        pairs = [(on[i][0], on[i + 1][0]) for i in range(0, len(on), 2)]
+        jt = re.search(r"&JoinType::(\w+)", body).group(1)
+        starts = [i for i in range(s, e) if "let expected = [" in lines[i]]
+        for k, es in enumerate(starts):
+            ee = next(i for i in range(es, e) if lines[i].strip() == "];")
+            header, rows = parse_table(lines[es:ee + 1])
+            upto = "\n".join(lines[s:es])
+            text = shared if "prepare_join_filter()" in upto else upto
+            cols, expr = parse_filter(text)
+            if not cols:   # column_indices defined once, reused by the second filter of the test
+                cols, _ = parse_filter(body)
+            mk = lambda t: {"batches": [{"names": [c[0] for c in t[1]], "columns": [c[1] for c in t[1]]}]}
+            out.append({"name": "%s#%d" % (name, k), "source": "%s:%d-%d" % (HJ, s + 1, e + 1), "join_type": jt, "left": mk(sides["left"]),
+                        "right": mk(sides["right"]), "on": pairs, "expected_header": header,
+                        "expected": [[None if c is None else int(c) for c in r] for r in rows], "ordered": False,
+                        "filter": {"column_indices": cols, "expr": expr}})
+    return out
+
+
 def join_cases():
     lines = read(HJ)
     src = "\n".join(lines)
@@ -110,6 +155,7 @@ def join_cases():
             "expected": [[None if c is None else int(c) for c in r] for r in rows],
             "ordered": ordered,
         })
+    cases += filter_join_cases(lines, helpers)
     # join_inner_one_two_parts_left: two build batches (hash_join.rs:1780-1837)
     s, e = find_fn(lines, "join_inner_one_two_parts_left")
     body = "\n".join(lines[s:e + 1])

@@ -10,7 +10,7 @@ import pytest
 
 import oracle
 from gpu_helpers import gpu_ctx, random_keys
-from util import assert_rows_equal, rows_of
+from util import assert_rows_equal, golden_filter, rows_of
 
 pytestmark = pytest.mark.gpu
 G = os.path.join(os.path.dirname(__file__), "golden")
@@ -38,11 +38,13 @@ def probe_path(request, monkeypatch):
     return request.param
 
 
-def gpu_join(ctx, jt, left, right, on, null_equals_null=False, left_schema=None, right_schema=None):
+def gpu_join(ctx, jt, left, right, on, null_equals_null=False, left_schema=None, right_schema=None, filter=None):
     import datafusion_upstream_b200 as df
     ls = left_schema or left[0].schema
     rs = right_schema or right[0].schema
     j = df.GpuHashJoinExec(ctx, ls, rs, on, df.JoinType(oracle.JOIN_TYPES[jt]), df.PartitionMode.CollectLeft, null_equals_null)
+    if filter is not None:
+        j.set_filter(*filter)
     out = j.execute(left, right)
     names = j.schema.names
     j.close()
@@ -58,7 +60,7 @@ def test_join_golden(ctx, case):
     left, right = batches(case["left"]), batches(case["right"])
     on = [(left[0].schema.names.index(l), right[0].schema.names.index(r)) for l, r in case["on"]]
     c = gpu_ctx(force_hash_collisions=True) if case.get("force_collisions") else ctx
-    out, names = gpu_join(c, JT[case["join_type"]], left, right, on)
+    out, names = gpu_join(c, JT[case["join_type"]], left, right, on, filter=golden_filter(case))   # incl. the join_*_with_filter tables
     assert names == case["expected_header"]
     assert_rows_equal(rows_of(out), [tuple(r) for r in case["expected"]], what=case["name"])
 
@@ -83,6 +85,45 @@ def test_join_fuzz_vs_oracle(ctx, jt, keys):
     out, _ = gpu_join(ctx, jt, left, right, on)
     want = oracle.hash_join(jt, left, right, on)
     assert_rows_equal(rows_of(out), rows_of(want), what=f"{jt} {keys}")
+
+
+@pytest.mark.parametrize("jt", ALL_TYPES)
+@pytest.mark.parametrize("keys", [["int64"], ["utf8", "int16"]], ids=lambda k: "+".join(k))
+def test_join_filter_fuzz_vs_oracle(ctx, jt, keys):
+    """Residual JoinFilter `l.id % 3 != r.id % 4 or r.s is null` (a predicate that is NULL-free but selective) through
+    probe_candidates / probe_commit, all 8 join types, several build and probe batches incl. an empty one; a second predicate
+    that evaluates to NULL for some pairs (NULL = not kept) and one that rejects everything."""
+    import pyarrow.compute as pc
+    rng = np.random.default_rng(sum(map(ord, jt + "".join(keys))) + 1)
+    left = [rand_side(rng, n, keys, 25, 0.1, "l") for n in (150, 1, 90)]
+    right = [rand_side(rng, n, keys, 30, 0.1, "r") for n in (400, 0, 333)]
+    on = [(i, i) for i in range(len(keys))]
+    nk = len(keys)
+    cols = [("left", nk), ("right", nk), ("right", nk + 1)]          # l.id, r.id, r.s
+    preds = [
+        lambda b: pc.or_(pc.not_equal(pc.bit_wise_and(b.column(0), 3), pc.bit_wise_and(b.column(1), 3)), pc.is_null(b.column(2))),
+        lambda b: pc.equal(b.column(2), pa.scalar("r3")),              # NULL where r.s is NULL
+        lambda b: pa.array(np.zeros(b.num_rows, bool)),
+    ]
+    for i, pred in enumerate(preds):
+        out, _ = gpu_join(ctx, jt, left, right, on, filter=(cols, pred))
+        want = oracle.hash_join(jt, left, right, on, filter=(cols, pred))
+        assert_rows_equal(rows_of(out), rows_of(want), what=f"{jt} {keys} predicate {i}")
+
+
+def test_join_filter_protocol_errors(ctx):
+    import datafusion_upstream_b200 as df
+    l = pa.record_batch([pa.array([1, 2, 3], pa.int64())], names=["a"])
+    r = pa.record_batch([pa.array([2, 3, 4], pa.int64())], names=["b"])
+    j = df.GpuHashJoinExec(ctx, l.schema, r.schema, [("a", "b")], df.JoinType.Left)
+    with pytest.raises(df.DfGpuError):
+        j.set_filter([("left", 5)], lambda b: None)                    # column out of range: Plan error
+    j.set_filter([("left", 0), ("right", 0)], None)
+    j.build([l])
+    with pytest.raises(df.DfGpuError) as e:
+        j.probe(r)                                                     # dfgpu_join_probe refuses a filtered join
+    assert "JoinFilter" in str(e.value)
+    j.close()
 
 
 @pytest.mark.parametrize("jt", ALL_TYPES)

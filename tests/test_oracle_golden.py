@@ -10,7 +10,7 @@ import pytest
 
 import oracle
 from oracle import AggSpec, OracleAgg
-from util import assert_rows_equal, rows_of
+from util import assert_rows_equal, golden_filter, rows_of
 
 G = os.path.join(os.path.dirname(__file__), "golden")
 JOINS = json.load(open(os.path.join(G, "hash_join.json")))
@@ -33,7 +33,7 @@ def test_join_golden(case, batch_size):
     left, right = batches(case["left"]), batches(case["right"])
     on = [(left[0].schema.names.index(l), right[0].schema.names.index(r)) for l, r in case["on"]]
     t = oracle.hash_join(JT[case["join_type"]], left, right, on, batch_size=batch_size,
-                         force_collisions=case.get("force_collisions", False))
+                         force_collisions=case.get("force_collisions", False), filter=golden_filter(case))
     assert t.schema.names == case["expected_header"]
     want = [tuple(r) for r in case["expected"]]
     assert_rows_equal(rows_of(t), want, ordered=case["ordered"], what=case["name"])

@@ -78,3 +78,20 @@ def assert_tables_equal(got, want, key_cols=None, rel=1e-9, ordered=False, check
         assert gt == wt, f"{what}: schema types {gt} != {wt}"
         assert got.schema.names == want.schema.names, f"{what}: names {got.schema.names} != {want.schema.names}"
     assert_rows_equal(rows_of(got), rows_of(want), key_cols, rel, ordered, what)
+
+
+def golden_filter(case):
+    """The JoinFilter of a golden join case as (column_indices, predicate over the intermediate batch), or None:
+    `column <op> literal | column` over Int32 (hash_join.rs `prepare_join_filter` and the *_with_filter tests)."""
+    import pyarrow as pa
+    import pyarrow.compute as pc
+    f = case.get("filter")
+    if not f:
+        return None
+    ops = {"Gt": pc.greater, "NotEq": pc.not_equal, "Lt": pc.less, "Eq": pc.equal, "GtEq": pc.greater_equal, "LtEq": pc.less_equal}
+    e = f["expr"]
+
+    def predicate(batch):
+        rhs = pa.scalar(e["rhs"]["lit"], pa.int32()) if "lit" in e["rhs"] else batch.column(e["rhs"]["col"])
+        return ops[e["op"]](batch.column(e["lhs"]), rhs)
+    return [(s, i) for s, i in f["column_indices"]], predicate
