@@ -86,7 +86,7 @@ SYMBOLS = [
     "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter", "dfgpu_batch_eval_decimal",
     "dfgpu_coalescer_create", "dfgpu_coalescer_push", "dfgpu_coalescer_finish", "dfgpu_coalescer_destroy",
     "dfgpu_partition_i64_noalloc", "dfgpu_agg_exchange_virtual",
-    "dfgpu_join_set_filter", "dfgpu_join_probe_candidates", "dfgpu_join_probe_commit",
+    "dfgpu_agg_emit_first", "dfgpu_join_set_filter", "dfgpu_join_probe_candidates", "dfgpu_join_probe_commit",
 ]
 
 _lib = None
@@ -143,6 +143,7 @@ def lib():
     L.dfgpu_agg_num_groups.argtypes = [P, C.POINTER(C.c_int64)]
     L.dfgpu_agg_emit.argtypes = [P, C.POINTER(P)]
     L.dfgpu_agg_emit_arrow.argtypes = [P, P, P]
+    L.dfgpu_agg_emit_first.argtypes = [P, C.c_int64, C.POINTER(P)]
     L.dfgpu_agg_metrics.argtypes = [P, C.POINTER(Metrics)]
     L.dfgpu_agg_destroy.argtypes = [P]
     L.dfgpu_join_create.argtypes = [P, C.c_int32, C.c_int32, C.c_int32, P, P, C.POINTER(C.c_int32), C.POINTER(C.c_int32),

@@ -12,6 +12,7 @@ void agg_push(dfgpu_agg &a, const Batch &batch);
 void agg_push_host(dfgpu_agg &a, const ArrowArray *batch);
 void agg_flush_pending(dfgpu_agg &a);
 Batch *agg_emit(dfgpu_agg &a);
+Batch *agg_emit_first(dfgpu_agg &a, int64_t n);
 const Schema &agg_out_schema(const dfgpu_agg &a);
 const Schema &agg_in_schema(const dfgpu_agg &a);
 Ctx *agg_ctx(const dfgpu_agg &a);
@@ -381,6 +382,12 @@ dfgpu_status dfgpu_agg_emit(dfgpu_agg *agg, dfgpu_batch **out) {
     DF_TRY
     DF_CUDA(cudaSetDevice(agg_ctx(*agg)->device));
     *out = agg_emit(*agg);
+    DF_CATCH
+}
+dfgpu_status dfgpu_agg_emit_first(dfgpu_agg *agg, int64_t n, dfgpu_batch **out) {
+    DF_TRY
+    DF_CUDA(cudaSetDevice(agg_ctx(*agg)->device));
+    *out = agg_emit_first(*agg, n);
     DF_CATCH
 }
 dfgpu_status dfgpu_agg_emit_arrow(dfgpu_agg *agg, ArrowArray *out_array, ArrowSchema *out_schema) {

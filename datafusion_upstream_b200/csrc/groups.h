@@ -80,6 +80,7 @@ class GroupTable {
     const uint32_t *ngroups_dev() const { return tv_.ngroups; }
     std::vector<ColRef> emit_keys(int64_t G);  // key columns in gid order (types = key_types)
     void reset();
+    void clear_shrink();   // reset + release every buffer (capacity 0)
     size_t device_bytes() const;
     KeyMode mode() const { return mode_; }
     void check_overflow();

@@ -358,6 +358,12 @@ class GpuAggregateExec:
         N.check(N.lib().dfgpu_agg_emit(self.h, C.byref(h)))
         return DeviceBatch(self.ctx, h)
 
+    def emit_first(self, n: int) -> pa.RecordBatch:
+        """emit(EmitTo::First(n)) (groups_accumulator.rs:24-58): n groups leave the operator, Partial mode only."""
+        h = C.c_void_p()
+        N.check(N.lib().dfgpu_agg_emit_first(self.h, n, C.byref(h)))
+        return DeviceBatch(self.ctx, h).to_arrow()
+
     def emit(self) -> pa.RecordBatch:
         """emit(EmitTo::All) (row_hash.rs:626-662)."""
         return self.emit_device().to_arrow()

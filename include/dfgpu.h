@@ -218,6 +218,13 @@ dfgpu_status dfgpu_agg_exchange_virtual(dfgpu_agg *const *aggs, int32_t n);
  * early emit (row_hash.rs:723-734) so it can be called mid-stream in Partial mode. */
 dfgpu_status dfgpu_agg_emit(dfgpu_agg *agg, dfgpu_batch **out);
 dfgpu_status dfgpu_agg_emit_arrow(dfgpu_agg *agg, struct ArrowArray *out_array, struct ArrowSchema *out_schema);
+/* emit(EmitTo::First(n)) (expr/src/groups_accumulator.rs:24-58; the early emit of row_hash.rs:723-734, where n is a multiple
+ * of batch_size): n of the groups accumulated so far leave the operator (fewer when fewer remain), the others stay queued for
+ * the next call; rows pushed in between start new partial states.  Partial mode only - there a key may be emitted more than
+ * once and the Final stage re-merges.  Group ids on the device are dense but not first-seen ordered, so which n groups come
+ * out is the operator's choice; streaming emission over sorted input (aggregates/order/) is not offered
+ * (DFGPU_NOT_IMPLEMENTED outside Partial mode) and such plans stay on the CPU.  dfgpu_agg_emit returns whatever is left. */
+dfgpu_status dfgpu_agg_emit_first(dfgpu_agg *agg, int64_t n, dfgpu_batch **out);
 dfgpu_status dfgpu_agg_metrics(const dfgpu_agg *agg, dfgpu_metrics *out);
 void dfgpu_agg_destroy(dfgpu_agg *agg);
 

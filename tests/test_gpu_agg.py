@@ -242,6 +242,55 @@ def test_early_emit_under_memory_limit():
     ctx.close(); ctx2.close()
 
 
+def test_early_emit_releases_memory():
+    """A high-cardinality spike followed by low-cardinality batches under a memory limit: after the early emit the operator must be
+    back under its limit (the reference clear_shrink()s, row_hash.rs:680, 708-712), so the small batches - fewer than batch_size
+    groups, which cannot trigger another early emit - go through instead of raising ResourcesExhausted."""
+    ctx = gpu_ctx(memory_limit=1 << 20, batch_size=64, chunk_rows=20_000)
+    rng = np.random.default_rng(10)
+    spike = pa.record_batch([pa.array(rng.integers(0, 100_000, 60_000), pa.int64()), pa.array(rng.integers(0, 9, 60_000), pa.int64())], names=["k", "v"])
+    small = [pa.record_batch([pa.array(rng.integers(0, 20, 5_000), pa.int64()), pa.array(rng.integers(0, 9, 5_000), pa.int64())], names=["k", "v"]) for _ in range(4)]
+    specs = [("sum", "v", "s", None), ("count", None, "c", None)]
+    st = gpu_agg(ctx, "partial", [spike] + small, ["k"], specs)
+    ctx2 = gpu_ctx()
+    fin = gpu_agg(ctx2, "final", [st], [0], [(f, None, nm, None) for f, _, nm, _ in specs])
+    assert_tables_equal(fin, oracle_agg("single", [spike] + small, ["k"], specs), key_cols=[0])
+    ctx.close(); ctx2.close()
+
+
+@pytest.mark.parametrize("keys", [["int64"], ["utf8", "int32"]], ids=lambda k: "+".join(k))
+def test_emit_first_n(ctx, keys):
+    """emit(EmitTo::First(n)) (groups_accumulator.rs:24-58) in Partial mode: n groups at a time, pushes in between, emit() for the
+    rest; the union of everything emitted, re-merged by Final, is the Single result.  Outside Partial mode: NotImplemented."""
+    import datafusion_upstream_b200 as df
+    rng = np.random.default_rng(21)
+    specs = [("sum", "i", "s", None), ("count", None, "c", None), ("avg", "d", "a", None), ("min", "f", "m", None)]
+    bs = [make_table(rng, n, keys, 700, 0.05, 0.1) for n in (5000, 3000, 4000)]
+    gk = [f"k{i}" for i in range(len(keys))]
+    exprs = [df.AggregateExpr(df.AggFunc[f.capitalize()], a, nm) for f, a, nm, _ in specs]
+    op = df.GpuAggregateExec(ctx, df.AggregateMode.Partial, bs[0].schema, gk, exprs)
+    parts = []
+    op.push(bs[0])
+    parts.append(op.emit_first(100)); assert parts[-1].num_rows == 100
+    parts.append(op.emit_first(64)); assert parts[-1].num_rows == 64
+    op.push(bs[1])                                   # new partial states next to the queued remainder
+    parts.append(op.emit_first(10_000))              # more than the queue holds: what is left of it
+    assert 0 < parts[-1].num_rows < 10_000
+    op.push(bs[2])
+    parts.append(op.emit_first(5))
+    parts.append(op.emit())
+    op.close()
+    assert all(p.schema == parts[0].schema for p in parts)
+    fin = gpu_agg(ctx, "final", parts, list(range(len(keys))), [(f, None, nm, None) for f, _, nm, _ in specs])
+    assert_tables_equal(fin, oracle_agg("single", bs, gk, specs), key_cols=list(range(len(keys))))
+    single = df.GpuAggregateExec(ctx, df.AggregateMode.Single, bs[0].schema, gk, exprs)
+    single.push(bs[0])
+    with pytest.raises(df.DfGpuError) as e:
+        single.emit_first(10)
+    assert e.value.kind == "NotImplemented"
+    single.close()
+
+
 def test_not_implemented_and_plan_errors(ctx):
     import datafusion_upstream_b200 as df
     b = pa.record_batch([pa.array([1], pa.int64()), pa.array(["x"])], names=["k", "s"])
