@@ -86,7 +86,7 @@ SYMBOLS = [
     "dfgpu_nccl_get_unique_id", "dfgpu_exchange_all_gather", "dfgpu_batch_project", "dfgpu_agg_exchange", "dfgpu_batch_filter", "dfgpu_batch_eval_decimal",
     "dfgpu_coalescer_create", "dfgpu_coalescer_push", "dfgpu_coalescer_finish", "dfgpu_coalescer_destroy",
     "dfgpu_partition_i64_noalloc", "dfgpu_agg_exchange_virtual",
-    "dfgpu_agg_emit_first", "dfgpu_join_set_filter", "dfgpu_join_probe_candidates", "dfgpu_join_probe_commit",
+    "dfgpu_agg_emit_first", "dfgpu_hash_contract", "dfgpu_join_set_filter", "dfgpu_join_probe_candidates", "dfgpu_join_probe_commit",
 ]
 
 _lib = None
@@ -104,6 +104,7 @@ def lib():
     P = C.c_void_p
     L.dfgpu_last_error.restype = C.c_char_p
     L.dfgpu_version.restype = C.c_char_p
+    L.dfgpu_hash_contract.restype = C.c_int32
     L.dfgpu_options_default.argtypes = [C.POINTER(Options)]
     L.dfgpu_ctx_create.argtypes = [C.POINTER(Options), C.POINTER(P)]
     L.dfgpu_ctx_destroy.argtypes = [P]

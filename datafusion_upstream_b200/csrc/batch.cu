@@ -457,6 +457,16 @@ static const void *upload(Ctx *ctx, DevCol &c, const void *src, size_t bytes, bo
     // 16 bytes of slack so vector loads at the tail stay in bounds
     BufRef b = make_buf(ctx, bytes + 16);
     DF_CUDA(cudaMemcpyAsync(b->ptr, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    // A pageable source is staged by the driver before cudaMemcpyAsync returns; a pinned (or registered) one is read by the DMA
+    // engine later.  Inputs are borrowed for the duration of the call only, so batch_import waits for such copies before it returns.
+    if (bytes >= (64 << 10) || !ctx->import_pinned_pending) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, src) == cudaSuccess) {
+            if (at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged) ctx->import_pinned_pending = true;
+        } else {
+            cudaGetLastError();
+        }
+    }
     ctx->h2d_bytes += (int64_t)bytes;
     c.owned.push_back(b);
     return b->ptr;
@@ -545,6 +555,13 @@ Batch *batch_import(Ctx *ctx, const ArrowArray *arr, const Schema &schema, bool 
         const ArrowArray *ch = arr->children[i];
         if (ch->length != arr->length) fail(DFGPU_INTERNAL, "column length mismatch in RecordBatch");
         b->cols.push_back(import_array(ctx, ch, schema.fields[(size_t)i], on_device));
+    }
+    if (ctx->import_pinned_pending) {
+        // the caller may release or reuse its (pinned) buffers as soon as this call returns: the copies must have read them
+        ctx->import_pinned_pending = false;
+        if (!ctx->import_event) DF_CUDA(cudaEventCreateWithFlags(&ctx->import_event, cudaEventDisableTiming));
+        DF_CUDA(cudaEventRecord(ctx->import_event, ctx->stream));
+        DF_CUDA(cudaEventSynchronize(ctx->import_event));
     }
     return b.release();
 }

@@ -59,6 +59,7 @@ void ctx_release(Ctx *c) {
     c->bufs.trim(c->stream);
     cudaStreamSynchronize(c->stream);
     ctx_destroy_nccl(c);
+    if (c->import_event) cudaEventDestroy(c->import_event);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -96,7 +97,8 @@ using namespace dfgpu;
 extern "C" {
 
 const char *dfgpu_last_error(void) { return dfgpu::last_error().c_str(); }
-const char *dfgpu_version(void) { return "dfgpu 0.1 (sm_100a)"; }
+const char *dfgpu_version(void) { return "dfgpu 0.2 (sm_100a)"; }
+int32_t dfgpu_hash_contract(void) { return 1; }   // "dfhash v1" (device.cuh): mix64 = splitmix64 finaliser, combine_hashes as hash_utils.rs:38-41
 
 void dfgpu_options_default(dfgpu_options *o) {
     memset(o, 0, sizeof *o);

@@ -136,6 +136,8 @@ struct dfgpu_ctx {
     dfgpu::PinnedPool pinned;
     dfgpu::BufCache bufs;
     uint64_t *flush_dummy = nullptr;
+    bool import_pinned_pending = false;   // batch_import queued a copy out of pinned host memory (batch.cu upload())
+    cudaEvent_t import_event = nullptr;
     std::atomic<int> refs{1};  // the creator's handle + every batch / operator created on this ctx
     // optional per-kernel CUDA-event timing (bench.py roofline): name -> (events, launches)
     bool profiling = false;

@@ -94,6 +94,12 @@ typedef struct dfgpu_metrics {     /* BaselineMetrics + BuildProbeJoinMetrics
 
 const char *dfgpu_last_error(void);
 const char *dfgpu_version(void);
+/* Identifies the row hash behind dfgpu_partition_hash / dfgpu_exchange_* / the join ("dfhash v1" = 1).  It is NOT ahash with
+ * DataFusion's fixed seeds (repartition/mod.rs:115), so rows land in other partitions than BatchPartitioner would put them:
+ * a plan must not pair a stream partitioned by this library with one partitioned by the CPU RepartitionExec (both inputs of
+ * a Partitioned HashJoinExec, or Partial -> Final across an exchange).  The shim's rule asserts that both sides of such a
+ * pair carry the same contract (rust/datafusion-gpu/src/rule.rs). */
+int32_t dfgpu_hash_contract(void);
 
 /* ---- context -------------------------------------------------------------------------- */
 void dfgpu_options_default(dfgpu_options *opts);
