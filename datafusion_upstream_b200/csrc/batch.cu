@@ -265,8 +265,44 @@ void BufCache::trim(cudaStream_t st) {
     cached = 0;
 }
 
+// ---- DFGPU_GUARD=1: red zones ----------------------------------------------------------------------
+// compute-sanitizer is not available on every box; this is the library's own out-of-bounds-write detector.  Each
+// buffer is allocated exactly (no size classes), with GUARD_ZONE bytes of 0xA5 before and after; the zones are
+// checked on the device when the buffer is freed and the verdict is read at dfgpu_ctx_synchronize,
+// dfgpu_batch_export and context teardown.  tests: DFGPU_GUARD=1 python -m pytest -m gpu
+static const size_t GUARD_ZONE = 256;
+__global__ void k_guard_fill(uint8_t *front, uint8_t *back) {
+    front[threadIdx.x] = 0xA5;
+    back[threadIdx.x] = 0xA5;
+}
+__global__ void k_guard_check(const uint8_t *front, const uint8_t *back, unsigned long long bytes, unsigned long long *words) {
+    bool bad = front[threadIdx.x] != 0xA5 || back[threadIdx.x] != 0xA5;
+    if (__syncthreads_or(bad) && threadIdx.x == 0)
+        if (atomicAdd(&words[0], 1ull) == 0) words[1] = bytes;
+}
+void guard_poll(Ctx *ctx) {
+    if (!ctx->guard) return;
+    unsigned long long w[2] = {0, 0};
+    DF_CUDA(cudaMemcpyAsync(w, ctx->guard_words, sizeof w, cudaMemcpyDeviceToHost, ctx->stream));
+    DF_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (w[0]) fail(DFGPU_INTERNAL, "DFGPU_GUARD: " + std::to_string(w[0]) + " buffer(s) were written out of bounds; the first had " +
+                                       std::to_string(w[1]) + " bytes");
+}
+
 DevBuf::DevBuf(Ctx *c, size_t n, bool zero) : ctx(c), bytes(n) {
     if (n == 0) return;
+    if (c->guard) {
+        uint8_t *raw = nullptr;
+        cudaError_t ge = cudaMallocAsync((void **)&raw, n + 2 * GUARD_ZONE, c->stream);
+        if (ge != cudaSuccess) {
+            cudaGetLastError();
+            fail(DFGPU_RESOURCES_EXHAUSTED, "Resources exhausted: failed to allocate " + std::to_string(n) + " bytes of device memory: " + cudaGetErrorString(ge));
+        }
+        ptr = raw + GUARD_ZONE;
+        k_guard_fill<<<1, (int)GUARD_ZONE, 0, c->stream>>>(raw, raw + GUARD_ZONE + n);
+        if (zero) DF_CUDA(cudaMemsetAsync(ptr, 0, n, c->stream));
+        return;
+    }
     cls = BufCache::size_class(n);
     if (cls) ptr = c->bufs.take(cls);
     cudaError_t e = cudaSuccess;
@@ -289,6 +325,12 @@ DevBuf::DevBuf(Ctx *c, size_t n, bool zero) : ctx(c), bytes(n) {
 }
 DevBuf::~DevBuf() {
     if (!ptr || parent) return;
+    if (ctx->guard) {
+        uint8_t *raw = (uint8_t *)ptr - GUARD_ZONE;
+        k_guard_check<<<1, (int)GUARD_ZONE, 0, ctx->stream>>>(raw, raw + GUARD_ZONE + bytes, (unsigned long long)bytes, ctx->guard_words);
+        cudaFreeAsync(raw, ctx->stream);
+        return;
+    }
     if (cls && ctx->bufs.give(cls, ptr)) return;
     cudaFreeAsync(ptr, ctx->stream);
 }

@@ -1,6 +1,7 @@
 // capi.cu — the extern "C" boundary (include/dfgpu.h): context, batches, create_hashes and the
 // aggregation operator.  Join and repartition entry points live in join.cu / partition.cu.
 #include <nccl.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include "device.cuh"
 #include "groups.h"
@@ -52,12 +53,23 @@ __global__ void k_create_hashes(HashCols hc, uint64_t seed, int force_collisions
         out[i] = h;
     }
 }
+NvtxRange::NvtxRange(const char *name) { nvtxRangePushA(name); }
+NvtxRange::~NvtxRange() { nvtxRangePop(); }
 void ctx_release(Ctx *c) {
     if (c->refs.fetch_sub(1) != 1) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     c->bufs.trim(c->stream);
     cudaStreamSynchronize(c->stream);
+    if (c->guard) {  // no caller left to hand a status to: say it and stop the process, this is a debugging mode
+        unsigned long long w[2] = {0, 0};
+        cudaMemcpy(w, c->guard_words, sizeof w, cudaMemcpyDeviceToHost);
+        cudaFree(c->guard_words);
+        if (w[0]) {
+            fprintf(stderr, "DFGPU_GUARD: %llu buffer(s) were written out of bounds; the first had %llu bytes\n", w[0], w[1]);
+            abort();
+        }
+    }
     ctx_destroy_nccl(c);
     if (c->import_event) cudaEventDestroy(c->import_event);
     cudaStreamDestroy(c->stream);
@@ -81,7 +93,7 @@ void create_hashes_device(Ctx *ctx, const std::vector<const DevCol *> &cols, int
 
 using namespace dfgpu;
 
-#define DF_TRY try {
+#define DF_TRY try { dfgpu::NvtxRange _nvtx(__func__);
 #define DF_CATCH                                                   \
     }                                                              \
     catch (const dfgpu::Error &e) {                                \
@@ -145,6 +157,11 @@ dfgpu_status dfgpu_ctx_create(const dfgpu_options *opts, dfgpu_ctx **out) {
         size_t free_b = 0, total_b = 0;
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) c->bufs.limit = total_b / 3;
     }
+    if (const char *g = getenv("DFGPU_GUARD")) c->guard = atoi(g);
+    if (c->guard) {
+        DF_CUDA(cudaMalloc((void **)&c->guard_words, 16));
+        DF_CUDA(cudaMemset(c->guard_words, 0, 16));
+    }
     if (o.world > 1) ctx_init_nccl(c.get());
     *out = c.release();
     DF_CATCH
@@ -155,6 +172,8 @@ void dfgpu_ctx_destroy(dfgpu_ctx *ctx) {
 dfgpu_status dfgpu_ctx_synchronize(dfgpu_ctx *ctx) {
     DF_TRY
     DF_CUDA(cudaStreamSynchronize(ctx->stream));
+    guard_poll(ctx);
+    comm_poll(ctx);
     DF_CATCH
 }
 dfgpu_status dfgpu_ctx_set_profiling(dfgpu_ctx *ctx, int32_t enable) {
@@ -215,6 +234,7 @@ dfgpu_status dfgpu_batch_export(dfgpu_ctx *ctx, const dfgpu_batch *batch, ArrowA
     DF_TRY
     DF_CUDA(cudaSetDevice(ctx->device));
     batch_export(ctx, batch, out_array, out_schema);
+    guard_poll(ctx);
     DF_CATCH
 }
 int64_t dfgpu_batch_num_rows(const dfgpu_batch *b) { return b ? b->num_rows : 0; }

@@ -123,6 +123,7 @@ struct dfgpu_ctx {
     int64_t launches = 0;
     int64_t h2d_bytes = 0, d2h_bytes = 0, nvlink_bytes = 0;
     void *nccl_comm = nullptr;  // ncclComm_t
+    std::string nccl_error;     // sticky: an asynchronous NCCL error aborted the communicator (ncclCommAbort); every later collective fails with it
     // Receive window of the peer-memory exchange (partition.cu): cudaMalloc'd (IPC-exportable), mapped by every
     // peer of the communicator; peers[r] = this process' mapping of rank r's window.
     struct PeerWindow {
@@ -135,6 +136,9 @@ struct dfgpu_ctx {
     } win;
     dfgpu::PinnedPool pinned;
     dfgpu::BufCache bufs;
+    // DFGPU_GUARD=1 (debug): every DevBuf gets a 256-byte red zone either side, checked when it is freed; see batch.cu
+    int guard = 0;
+    unsigned long long *guard_words = nullptr;  // [0] = corrupted red zones seen, [1] = size of the first offender
     uint64_t *flush_dummy = nullptr;
     bool import_pinned_pending = false;   // batch_import queued a copy out of pinned host memory (batch.cu upload())
     cudaEvent_t import_event = nullptr;
@@ -190,6 +194,12 @@ struct KTimer {
     }
 };
 
+// NVTX range per ABI call and per operator phase (nsys / ncu --nvtx show them; free when no tool is attached)
+struct NvtxRange {
+    explicit NvtxRange(const char *name);
+    ~NvtxRange();
+};
+
 // DFGPU_TRACE=1: host-side timeline on stderr (microseconds since the previous trace point, any translation unit)
 inline void df_trace(const char *label) {
     static const bool on = getenv("DFGPU_TRACE") != nullptr;
@@ -201,6 +211,8 @@ inline void df_trace(const char *label) {
 }
 
 // communicator wrappers (partition.cu; NCCL is dlopen'd there): byte counts, ctx->stream
+void guard_poll(Ctx *ctx);  // DFGPU_GUARD=1: fail with DFGPU_INTERNAL if a freed buffer had a damaged red zone
+void comm_poll(Ctx *ctx);  // world > 1: raise (and make sticky) an asynchronous NCCL error; aborts the communicator
 void comm_all_gather(Ctx *ctx, const void *send, void *recv, size_t bytes_per_rank);
 void comm_group_start();
 void comm_group_end();

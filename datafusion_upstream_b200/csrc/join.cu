@@ -676,7 +676,7 @@ Batch *join_emit_unmatched(JoinOp &j) {
 }  // namespace dfgpu
 
 using namespace dfgpu;
-#define J_TRY try {
+#define J_TRY try { dfgpu::NvtxRange _nvtx(__func__);
 #define J_CATCH } catch (const dfgpu::Error &e) { dfgpu::set_last_error(e.msg); return e.code; } \
     catch (const std::exception &e) { dfgpu::set_last_error(std::string("Internal error: ") + e.what()); return DFGPU_INTERNAL; } \
     return DFGPU_OK;

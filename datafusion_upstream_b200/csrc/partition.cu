@@ -133,6 +133,8 @@ struct NcclApi {
     ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommGetAsyncError)(ncclComm_t, ncclResult_t *) = nullptr;
     ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
@@ -152,7 +154,7 @@ static NcclApi &nccl() {
 #define LOAD(f) \
     *(void **)(&api.f) = dlsym(api.lib, "nccl" #f); \
     if (!api.f) fail(DFGPU_NCCL, "libnccl lacks nccl" #f);
-        LOAD(GetUniqueId) LOAD(CommInitRank) LOAD(CommDestroy) LOAD(Send) LOAD(Recv) LOAD(GroupStart) LOAD(GroupEnd)
+        LOAD(GetUniqueId) LOAD(CommInitRank) LOAD(CommDestroy) LOAD(CommAbort) LOAD(CommGetAsyncError) LOAD(Send) LOAD(Recv) LOAD(GroupStart) LOAD(GroupEnd)
         LOAD(AllGather) LOAD(GetErrorString)
 #undef LOAD
     }
@@ -177,18 +179,40 @@ void ctx_destroy_nccl(Ctx *ctx) {
     if (ctx->nccl_comm) nccl().CommDestroy((ncclComm_t)ctx->nccl_comm);
     ctx->nccl_comm = nullptr;
 }
+// Asynchronous failures (a peer died, a link error) surface through ncclCommGetAsyncError, not through the enqueue calls.
+// Checked before every collective of this context: on an error the communicator is aborted - which unblocks kernels that
+// would otherwise wait for the dead peer for ever - and the error sticks to the context, so the operator fails with a
+// DFGPU_NCCL status instead of hanging (the reference's analogue: a failed input stream ends the plan with its Err).
+static void comm_check(Ctx *ctx) {
+    if (!ctx->nccl_error.empty()) fail(DFGPU_NCCL, ctx->nccl_error);
+    if (!ctx->nccl_comm) fail(DFGPU_NCCL, "NCCL error: no communicator (world > 1 requires a ncclUniqueId)");
+    ncclResult_t async = ncclSuccess;
+    ncclResult_t q = nccl().CommGetAsyncError((ncclComm_t)ctx->nccl_comm, &async);
+    if (q == ncclSuccess && (async == ncclSuccess || async == ncclInProgress)) return;
+    ctx->nccl_error = std::string("NCCL error (asynchronous): ") + nccl().GetErrorString(q != ncclSuccess ? q : async) + "; communicator aborted";
+    nccl().CommAbort((ncclComm_t)ctx->nccl_comm);
+    ctx->nccl_comm = nullptr;
+    fail(DFGPU_NCCL, ctx->nccl_error);
+}
+
+void comm_poll(Ctx *ctx) {
+    if (ctx->opts.world > 1) comm_check(ctx);
+}
 
 // thin communicator wrappers for the other translation units (fastagg.cu): byte-typed, on ctx->stream
 void comm_all_gather(Ctx *ctx, const void *send, void *recv, size_t bytes_per_rank) {
+    comm_check(ctx);
     DF_NCCL(nccl().AllGather(send, recv, bytes_per_rank, ncclChar, (ncclComm_t)ctx->nccl_comm, ctx->stream));
 }
 void comm_group_start() { DF_NCCL(nccl().GroupStart()); }
 void comm_group_end() { DF_NCCL(nccl().GroupEnd()); }
 void comm_send(Ctx *ctx, const void *p, size_t bytes, int peer) {
+    if (!ctx->nccl_error.empty() || !ctx->nccl_comm) comm_check(ctx);
     DF_NCCL(nccl().Send(p, bytes, ncclChar, peer, (ncclComm_t)ctx->nccl_comm, ctx->stream));
     if (peer != ctx->opts.rank) ctx->nvlink_bytes += (int64_t)bytes;
 }
 void comm_recv(Ctx *ctx, void *p, size_t bytes, int peer) {
+    if (!ctx->nccl_error.empty() || !ctx->nccl_comm) comm_check(ctx);
     DF_NCCL(nccl().Recv(p, bytes, ncclChar, peer, (ncclComm_t)ctx->nccl_comm, ctx->stream));
 }
 
@@ -388,6 +412,7 @@ Batch *exchange_all_to_all(Ctx *ctx, Batch *const *parts, const Schema &schema) 
         Batch *one[1] = {parts[0]};
         return batch_concat(ctx, one, 1);
     }
+    comm_check(ctx);
     ncclComm_t comm = (ncclComm_t)ctx->nccl_comm;
     cudaStream_t st = ctx->stream;
     // decode dictionaries; count rows / var bytes per destination
