@@ -133,7 +133,11 @@ struct dfgpu_ctx {
         int state = 0;  // 0 untried, 1 in use, -1 unavailable on some rank: NCCL send/recv instead
         struct Peer { uint64_t gen = 0; void *ptr = nullptr; } peers[64];
         void *scratch = nullptr;  // small device staging for the handle all-gather / barrier
-    } win;
+        // send arena only (pull model): bump allocator owned by one operator at a time
+        size_t used = 0;
+        const void *owner = nullptr;
+        std::vector<void *> retired;  // outgrown buffers some peer may still have mapped: freed at the next handle exchange
+    } win, swin;  // win: receive window (peers store into it); swin: send arena (peers load from it)
     dfgpu::PinnedPool pinned;
     dfgpu::BufCache bufs;
     // DFGPU_GUARD=1 (debug): every DevBuf gets a 256-byte red zone either side, checked when it is freed; see batch.cu
@@ -226,6 +230,17 @@ bool peer_window_prepare(Ctx *ctx, size_t need, void **peer_ptrs);
 void peer_push(Ctx *ctx, int n, const void *const *src, void *const *dst, const size_t *bytes);
 void peer_barrier(Ctx *ctx);
 void peer_window_destroy(Ctx *ctx);
+// Send arena (pull model of the record exchange).  An operator places what its peers will read - its partitioned key
+// pieces - in this rank's arena: cudaMalloc'd (IPC-exportable), kept across operators, grown locally.  arena_alloc is
+// local: bytes at a 256-byte aligned offset, or false when the arena belongs to another live operator (the caller then
+// uses pool memory and the push model); *moved is set when the arena was re-allocated and its live prefix copied, i.e.
+// pointers into it must be re-derived from arena_base() + offset.  arena_map is collective: gens[r] = arena generation
+// of rank r (gathered by the caller); handles travel only when some rank's arena grew since they were last exchanged.
+bool arena_alloc(Ctx *ctx, const void *owner, size_t bytes, size_t *off, bool *moved);
+void arena_release(Ctx *ctx, const void *owner);
+void *arena_base(Ctx *ctx);
+uint64_t arena_gen(Ctx *ctx);
+bool arena_map(Ctx *ctx, const uint64_t *gens, void **peer_ptrs);
 
 // device buffer allocated from the stream-ordered pool of ctx->stream
 struct DevBuf {

@@ -86,6 +86,7 @@ struct FaResult {
 class FastAgg {
   public:
     FastAgg(Ctx *ctx, const std::vector<FaOpSpec> &ops);
+    ~FastAgg();
     static bool kind_supported(int kind) { return kind != OP_MIN_I128 && kind != OP_MAX_I128 && kind < OP_AND_U64; }
     int SW() const { return SW_; }
     int seen_word() const { return seen_word_; }
@@ -123,7 +124,7 @@ class FastAgg {
     void push_part(const FaPlan &plan, int64_t n, int64_t algo_bytes);
     FaResult finalize_part();
     void reset_store();
-    struct Piece { BufRef keys, offs, hist; int64_t rows = 0; };
+    struct Piece { BufRef keys, offs, hist; int64_t rows = 0; int64_t arena_off = -1; /* >= 0: keys lie in the send arena (partition.cu) */ };
     // record exchange in phases, so that real ranks (collectives between the phases) and virtual ranks (loops) share them
     struct Xchg;
     bool count_only() const { return ops_.size() == 1 && ops_[0].kind == 1 /* OP_COUNT */ && nbits_ == 0 && SW_ == 1; }
@@ -132,6 +133,12 @@ class FastAgg {
     size_t xchg_plan(Xchg &x, const std::vector<uint8_t> &meta_all);                // from everybody's meta: what goes where; bytes my window needs
     void xchg_push(Xchg &x, void *const *windows);                                  // my runs -> the owners' windows
     void xchg_finish(Xchg &x, void *my_window, bool window_borrowed, const BufRef &meta_all_dev);  // pieces of what arrived; side groups
+    // pull model (count-only operators): nothing is copied; the merge reads every source's pieces where they lie.
+    // src[s * 3 + k] = stream k of rank s as this rank addresses it (peer mapping / plain pointer), recv = elements per piece
+    void xchg_finish_pull(Xchg &x, const uint64_t *const *src, const int64_t *recv, const BufRef &meta_all_dev);
+    BufRef arena_buf(size_t bytes, int64_t *arena_off);   // from the send arena when this operator may use it, else from the pool
+    void arena_refresh();                                 // the arena moved: re-derive the pieces' pointers
+    bool xpull_ = false;          // the exchange that ran was a pull between real ranks: finalize ends with the closing barrier
     std::vector<BufRef> xhold_;        // received window (virtual ranks), gathered meta, piece tables: alive until the merge ran
     BufRef xp_offs_, xp_hist_;         // [npieces][FA_P] of the received pieces (count-only operators)
     std::vector<const uint64_t *> xp_base_;

@@ -261,54 +261,81 @@ void peer_push(Ctx *ctx, int n, const void *const *src, void *const *dst, const 
     note_launch(ctx);
     DF_CUDA(cudaGetLastError());
 }
+static void window_scratch(dfgpu_ctx::PeerWindow &w) {
+    if (w.scratch) return;
+    if (cudaMalloc(&w.scratch, 8192) != cudaSuccess || cudaMemset(w.scratch, 0, 8192) != cudaSuccess)   // [0,1024) barrier, [1024,..) handles
+        fail(DFGPU_CUDA, "peer window: cannot allocate the staging buffer");
+}
 void peer_barrier(Ctx *ctx) {
     auto &w = ctx->win;
+    window_scratch(w);
     comm_all_gather(ctx, w.scratch, (uint8_t *)w.scratch + 256, 8);
 }
-void peer_window_destroy(Ctx *ctx) {
-    auto &w = ctx->win;
+static void window_destroy(dfgpu_ctx::PeerWindow &w) {
     for (auto &p : w.peers) if (p.ptr && p.ptr != w.buf) cudaIpcCloseMemHandle(p.ptr);
     for (auto &p : w.peers) p = {};
+    for (void *r : w.retired) cudaFree(r);
+    w.retired.clear();
     if (w.buf) cudaFree(w.buf);
     if (w.scratch) cudaFree(w.scratch);
     w.buf = w.scratch = nullptr;
     w.bytes = 0;
 }
-bool peer_window_prepare(Ctx *ctx, size_t need, void **peer_ptrs) {
-    auto &w = ctx->win;
-    const int W = ctx->opts.world, me = ctx->opts.rank;
-    if (w.state < 0 || W > 64) return false;
-    if (const char *e = getenv("DFGPU_EXCHANGE")) if (!strcmp(e, "nccl")) { w.state = -1; return false; }
-    // Every window is large enough and mapped already (`need` is the same number on every rank, so this is decided alike
-    // everywhere).  The caller's all-gather of the partition histograms, stream-ordered after whatever still read the
-    // windows, already was the barrier that frees them for the next round of stores.
-    if (w.state == 1 && need <= w.bytes) {
-        for (int r = 0; r < W; r++) peer_ptrs[r] = w.peers[r].ptr;
-        return true;
+void peer_window_destroy(Ctx *ctx) {
+    window_destroy(ctx->win);
+    window_destroy(ctx->swin);
+}
+
+// ---- send arena -------------------------------------------------------------------------------------
+void *arena_base(Ctx *ctx) { return ctx->swin.buf; }
+uint64_t arena_gen(Ctx *ctx) { return ctx->swin.gen; }
+bool arena_alloc(Ctx *ctx, const void *owner, size_t bytes, size_t *off, bool *moved) {
+    auto &w = ctx->swin;
+    *moved = false;
+    if (w.state < 0 || ctx->opts.world <= 1 || ctx->opts.world > 64) return false;
+    if (const char *e = getenv("DFGPU_EXCHANGE")) if (strcmp(e, "pull")) return false;   // "nccl" / "push": the push model
+    if (w.owner && w.owner != owner) return false;
+    if (!w.owner) w.used = 0;
+    const size_t at = (w.used + 255) & ~(size_t)255;
+    if (at + bytes > w.bytes) {
+        // grow locally; peers learn the new handle at the next exchange (the generation travels in the meta block)
+        const size_t nb = ((at + bytes) + (at + bytes) / 2 + ((size_t)1 << 20)) & ~(size_t)255;
+        void *nbuf = nullptr;
+        if (cudaMalloc(&nbuf, nb) != cudaSuccess) { cudaGetLastError(); return false; }
+        if (w.buf) {
+            if (w.owner && w.used) {
+                DF_CUDA(cudaMemcpyAsync(nbuf, w.buf, w.used, cudaMemcpyDeviceToDevice, ctx->stream));
+                *moved = true;
+            }
+            DF_CUDA(cudaStreamSynchronize(ctx->stream));
+            w.retired.push_back(w.buf);   // a peer may still have it mapped (not reading it: the closing barrier of the last exchange has passed)
+        }
+        w.buf = nbuf;
+        w.bytes = nb;
+        w.gen++;
     }
+    w.owner = owner;
+    *off = at;
+    w.used = at + bytes;
+    return true;
+}
+void arena_release(Ctx *ctx, const void *owner) {
+    auto &w = ctx->swin;
+    if (w.owner == owner) { w.owner = nullptr; w.used = 0; }
+}
+// Collective: every rank publishes the IPC handle and generation of its buffer of window `w` and maps the others'.
+// `ok` = this rank is able to take part; the result (false: peer mapping is unavailable, for good) is alike everywhere.
+static bool window_exchange_handles(Ctx *ctx, dfgpu_ctx::PeerWindow &w, bool ok, void **peer_ptrs) {
+    const int W = ctx->opts.world, me = ctx->opts.rank;
     cudaStream_t st = ctx->stream;
     struct Msg { cudaIpcMemHandle_t h; uint64_t gen; uint64_t ok; };  // 80 bytes
     static_assert(sizeof(Msg) == 80, "handle message layout");
-    bool ok = true;
-    if (!w.scratch) ok = cudaMalloc(&w.scratch, 8192) == cudaSuccess && cudaMemset(w.scratch, 0, 8192) == cudaSuccess;  // [0,1024) barrier, [1024,..) handles
+    window_scratch(w);
     Msg mine;
     memset(&mine, 0, sizeof mine);
-    void *retired = nullptr;
-    if (ok && need > w.bytes) {
-        // grow: everything queued on the old window (peers' pushes of the previous exchange were fenced by its barrier)
-        // the old window stays allocated until every peer has dropped its mapping of it (after the second gather)
-        DF_CUDA(cudaStreamSynchronize(st));
-        retired = w.buf;
-        w.buf = nullptr;
-        w.bytes = 0;
-        size_t nb = (need + need / 2 + ((size_t)1 << 20)) & ~(size_t)255;
-        if (cudaMalloc(&w.buf, nb) == cudaSuccess) { w.bytes = nb; w.gen++; }
-        else { cudaGetLastError(); ok = false; }
-    }
     if (ok && w.buf && cudaIpcGetMemHandle(&mine.h, w.buf) != cudaSuccess) { cudaGetLastError(); ok = false; }
     mine.gen = w.gen;
     mine.ok = ok ? 1 : 0;
-    if (!w.scratch) fail(DFGPU_CUDA, "peer window: cannot allocate the staging buffer");
     uint8_t *stage = (uint8_t *)w.scratch + 1024;             // [Msg mine][Msg all[W]]
     std::vector<Msg> all((size_t)W);
     auto gather = [&]() {
@@ -334,11 +361,57 @@ bool peer_window_prepare(Ctx *ctx, size_t need, void **peer_ptrs) {
     mine.ok = ok ? 1 : 0;
     gather();
     for (int r = 0; r < W; r++) ok = ok && all[(size_t)r].ok;
-    if (retired) cudaFree(retired);  // every rank is past its remapping loop
+    for (void *r : w.retired) cudaFree(r);  // every rank is past its remapping loop: nobody maps an outgrown buffer any more
+    w.retired.clear();
     if (!ok) { w.state = -1; return false; }
     w.state = 1;
     for (int r = 0; r < W; r++) peer_ptrs[r] = w.peers[r].ptr;
     return true;
+}
+bool peer_window_prepare(Ctx *ctx, size_t need, void **peer_ptrs) {
+    auto &w = ctx->win;
+    const int W = ctx->opts.world;
+    if (w.state < 0 || W > 64) return false;
+    if (const char *e = getenv("DFGPU_EXCHANGE")) if (!strcmp(e, "nccl")) { w.state = -1; return false; }
+    // Every window is large enough and mapped already (`need` is the same number on every rank, so this is decided alike
+    // everywhere).  The caller's all-gather of the partition histograms, stream-ordered after whatever still read the
+    // windows, already was the barrier that frees them for the next round of stores.
+    if (w.state == 1 && need <= w.bytes) {
+        for (int r = 0; r < W; r++) peer_ptrs[r] = w.peers[r].ptr;
+        return true;
+    }
+    bool ok = true;
+    if (need > w.bytes) {
+        // grow: everything queued on the old window (peers' pushes of the previous exchange were fenced by its barrier)
+        // the old window stays allocated until every peer has dropped its mapping of it (after the second gather)
+        DF_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (w.buf) w.retired.push_back(w.buf);
+        w.buf = nullptr;
+        w.bytes = 0;
+        size_t nb = (need + need / 2 + ((size_t)1 << 20)) & ~(size_t)255;
+        if (cudaMalloc(&w.buf, nb) == cudaSuccess) { w.bytes = nb; w.gen++; }
+        else { cudaGetLastError(); ok = false; }
+    }
+    return window_exchange_handles(ctx, w, ok, peer_ptrs);
+}
+bool arena_map(Ctx *ctx, const uint64_t *gens, void **peer_ptrs) {
+    auto &w = ctx->swin;
+    const int W = ctx->opts.world;
+    if (w.state < 0 || W > 64) return false;
+    // peers[r].gen (r == me included) is the generation of rank r's arena when handles were last exchanged: the same
+    // numbers on every rank, so every rank decides alike whether handles have to travel again.
+    bool stale = w.state != 1;
+    for (int r = 0; r < W; r++) stale = stale || w.peers[r].gen != gens[r];
+    if (!stale) {
+        for (int r = 0; r < W; r++) peer_ptrs[r] = w.peers[r].ptr;
+        return true;
+    }
+    bool ok = true;
+    if (!w.buf) {   // a rank that placed nothing yet still needs something to export
+        if (cudaMalloc(&w.buf, (size_t)1 << 20) == cudaSuccess) { w.bytes = (size_t)1 << 20; w.gen++; }
+        else { cudaGetLastError(); ok = false; }
+    }
+    return window_exchange_handles(ctx, w, ok, peer_ptrs);
 }
 
 // ---- exchange helpers --------------------------------------------------------------------------------

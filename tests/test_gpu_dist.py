@@ -155,9 +155,18 @@ def _worker_big(rank, world, port, n_rows, s2max, out_q):
         k = _big_keys(rank, n_rows)
         b = pa.record_batch([pa.array(k, pa.int64())], names=["k"])
         res = []
-        for specs in ([("count", None, "c")], [("count", None, "c"), ("sum", "k", "s")]):   # partition path (key pieces) / cache path (records)
+        count, count_sum = [("count", None, "c")], [("count", None, "c"), ("sum", "k", "s")]   # partition path (key pieces) / cache path (records)
+        # count-only operators: the owner's merge reads the peers' key pieces over NVLink (pull; twice, the second time in two pushes
+        # so that the send arena holds two pieces and has to grow), runs copied into the owner's window (push), NCCL send / recv
+        for specs, model, pushes in ((count, "pull", 1), (count, "pull", 2), (count, "push", 1), (count_sum, "pull", 1), (count, "nccl", 1)):
+            os.environ["DFGPU_EXCHANGE"] = model
             op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, b.schema, ["k"], [df.AggregateExpr(df.AggFunc[f.capitalize()], a, nm) for f, a, nm in specs])
-            op.push(b)
+            if pushes == 1:
+                op.push(b)
+            else:
+                cut = (2 * n_rows) // 3 + 1000 * rank
+                op.push(b.slice(0, cut))
+                op.push(b.slice(cut))
             op.exchange()
             out = op.emit()
             op.close()
@@ -200,7 +209,7 @@ def test_multi_gpu_count_star_20m_rows_per_rank(world, s2max):
     uk, uc = np.unique(allk, return_counts=True)
     with np.errstate(over="ignore"):
         want_cks = int((uk.view(np.uint64) * np.uint64(0xBF58476D1CE4E5B9) * uc.astype(np.uint64)).sum(dtype=np.uint64))
-    for variant in range(2):
+    for variant in range(5):
         G = sum(r[variant][0] for r in res)
         rows = sum(r[variant][1] for r in res)
         cks = sum(r[variant][2] for r in res) % (1 << 64)

@@ -81,12 +81,16 @@ def test_general_accumulators_over_record_pieces(monkeypatch, world, hook):
         ctx.close()
 
 
+@pytest.mark.parametrize("model", ["pull", "push"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("modes", ["all_partition", "all_cache", "mixed"])
-def test_count_star_key_and_record_pieces(monkeypatch, world, modes):
+def test_count_star_key_and_record_pieces(monkeypatch, world, modes, model):
     """COUNT(*): ranks on the partition path send bare keys + hot keys, ranks on the cache path send records; the owner merges both
-    kinds of pieces (k_hp_merge).  NULL and all-ones keys (side groups) end up on rank 0."""
+    kinds of pieces (k_hp_merge).  NULL and all-ones keys (side groups) end up on rank 0.  model = pull: the owner's merge reads the
+    other ranks' streams where they lie (the default between real ranks: NVLink loads); push: runs are copied into the owner's
+    window first (the fallback, and the path of operators with other accumulators)."""
     import datafusion_upstream_b200 as df
+    monkeypatch.setenv("DFGPU_EXCHANGE", model)
     ctx = gpu_ctx()
     try:
         rng = np.random.default_rng(100 + world)
@@ -114,6 +118,7 @@ def test_count_star_key_and_record_pieces(monkeypatch, world, modes):
             op.close()
         assert "k_hp_merge" in names, names
         assert ("k_hp_part1" in names) == (modes != "all_cache")
+        assert ("stage:record_exchange_peer_push" in names) == (model == "push"), names
         check_union(outs, shards, ["k"], COUNT, 1)
         null_rows = [i for i, o in enumerate(outs) if o.num_rows and o.column(0).null_count]
         assert null_rows == [0]
