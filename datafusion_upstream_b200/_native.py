@@ -79,7 +79,7 @@ SYMBOLS = [
     "dfgpu_ctx_synchronize", "dfgpu_ctx_set_profiling", "dfgpu_ctx_profile_json", "dfgpu_ctx_stream", "dfgpu_ctx_kernel_launches", "dfgpu_host_alloc", "dfgpu_host_free",
     "dfgpu_batch_import", "dfgpu_batch_export", "dfgpu_batch_num_rows", "dfgpu_batch_num_columns", "dfgpu_batch_schema",
     "dfgpu_batch_concat", "dfgpu_batch_slice", "dfgpu_batch_free", "dfgpu_create_hashes", "dfgpu_agg_create",
-    "dfgpu_agg_output_schema", "dfgpu_agg_push", "dfgpu_agg_push_arrow", "dfgpu_agg_num_groups", "dfgpu_agg_emit",
+    "dfgpu_agg_output_schema", "dfgpu_agg_push", "dfgpu_agg_push_arrow", "dfgpu_agg_push_arrow_batches", "dfgpu_agg_num_groups", "dfgpu_agg_emit",
     "dfgpu_agg_emit_arrow", "dfgpu_agg_metrics", "dfgpu_agg_destroy", "dfgpu_join_create", "dfgpu_join_output_schema",
     "dfgpu_join_build_push", "dfgpu_join_build_finish", "dfgpu_join_probe", "dfgpu_join_emit_unmatched",
     "dfgpu_join_metrics", "dfgpu_join_destroy", "dfgpu_partition_hash", "dfgpu_exchange_all_to_all",
@@ -141,6 +141,7 @@ def lib():
     L.dfgpu_agg_output_schema.argtypes = [P, P]
     L.dfgpu_agg_push.argtypes = [P, P]
     L.dfgpu_agg_push_arrow.argtypes = [P, P]
+    L.dfgpu_agg_push_arrow_batches.argtypes = [P, C.POINTER(P), C.c_int32]
     L.dfgpu_agg_num_groups.argtypes = [P, C.POINTER(C.c_int64)]
     L.dfgpu_agg_emit.argtypes = [P, C.POINTER(P)]
     L.dfgpu_agg_emit_arrow.argtypes = [P, P, P]

@@ -11,6 +11,7 @@ namespace dfgpu {
 dfgpu_agg *agg_create(Ctx *ctx, int mode, const Schema &in, const int32_t *group_cols, int n_group, const dfgpu_agg_desc *descs, int n_aggs);
 void agg_push(dfgpu_agg &a, const Batch &batch);
 void agg_push_host(dfgpu_agg &a, const ArrowArray *batch);
+void agg_push_host_many(dfgpu_agg &a, const ArrowArray *const *batches, int n);
 void agg_flush_pending(dfgpu_agg &a);
 Batch *agg_emit(dfgpu_agg &a);
 Batch *agg_emit_first(dfgpu_agg &a, int64_t n);
@@ -379,6 +380,14 @@ dfgpu_status dfgpu_agg_push_arrow(dfgpu_agg *agg, const ArrowArray *batch) {
     Ctx *ctx = agg_ctx(*agg);
     DF_CUDA(cudaSetDevice(ctx->device));
     agg_push_host(*agg, batch);
+    DF_CATCH
+}
+dfgpu_status dfgpu_agg_push_arrow_batches(dfgpu_agg *agg, const ArrowArray *const *batches, int32_t n) {
+    DF_TRY
+    if (n < 0 || (n > 0 && !batches)) fail(DFGPU_INTERNAL, "push_arrow_batches: null batch array");
+    Ctx *ctx = agg_ctx(*agg);
+    DF_CUDA(cudaSetDevice(ctx->device));
+    agg_push_host_many(*agg, batches, n);
     DF_CATCH
 }
 dfgpu_status dfgpu_agg_num_groups(dfgpu_agg *agg, int64_t *out) {

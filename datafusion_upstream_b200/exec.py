@@ -335,6 +335,40 @@ class GpuAggregateExec:
                     C.CFUNCTYPE(None, C.POINTER(N.ArrowArray))(a.release)(C.byref(a))
                 N.release_schema(s)
 
+    def export_batches(self, batches: Sequence[pa.RecordBatch]):
+        """Arrow C Data Interface structs of host batches, ready for push_exported (what a Rust shim holds anyway: its
+        RecordBatches are FFI-exportable without a copy).  Keep the returned object alive until push_exported returned."""
+        arrs = []
+        for b in batches:
+            if b.schema.types != self.input_schema.types:
+                raise N.DfGpuError(1, f"Internal error: pushed batch schema {b.schema.types} != operator input schema {self.input_schema.types}")
+            a, s = N.ArrowArray(), N.ArrowSchema()
+            b._export_to_c(C.addressof(a), C.addressof(s))
+            N.release_schema(s)
+            arrs.append(a)
+        ptrs = (C.c_void_p * len(arrs))(*[C.addressof(a) for a in arrs])
+        return arrs, ptrs
+
+    def push_exported(self, exported):
+        """dfgpu_agg_push_arrow_batches: all batches of export_batches() in one call."""
+        arrs, ptrs = exported
+        N.check(N.lib().dfgpu_agg_push_arrow_batches(self.h, ptrs, len(arrs)))
+
+    @staticmethod
+    def release_exported(exported):
+        arrs, _ = exported
+        for a in arrs:
+            if a.release:
+                C.CFUNCTYPE(None, C.POINTER(N.ArrowArray))(a.release)(C.byref(a))
+
+    def push_many(self, batches: Sequence[pa.RecordBatch]):
+        """n host batches in one ABI call (dfgpu_agg_push_arrow_batches): same result as push() on each, in order."""
+        ex = self.export_batches(batches)
+        try:
+            self.push_exported(ex)
+        finally:
+            self.release_exported(ex)
+
     def exchange(self):
         """Collective: fused Partial -> RepartitionExec(Hash) -> FinalPartitioned (dfgpu_agg_exchange).  After it,
         emit() returns the finished groups of the keys this rank owns.  Raises DfGpuError(NotImplemented) when the

@@ -204,6 +204,12 @@ dfgpu_status dfgpu_agg_output_schema(const dfgpu_agg *agg, struct ArrowSchema *o
 /* group_aggregate_batch (row_hash.rs:524-613): GroupValues::intern + update_batch/merge_batch */
 dfgpu_status dfgpu_agg_push(dfgpu_agg *agg, const dfgpu_batch *batch);
 dfgpu_status dfgpu_agg_push_arrow(dfgpu_agg *agg, const struct ArrowArray *batch);
+/* n host batches in one call: the same result as n dfgpu_agg_push_arrow calls in that order.  The reference's stream
+ * hands the operator one 8192-row RecordBatch at a time (row_hash.rs:423-470); a shim that has several ready (a
+ * buffered channel, a CoalesceBatchesExec it replaced) passes them together and the library packs them into its
+ * pinned arena with several host threads instead of one (one thread packs ~10 GB/s; PCIe 5 takes 55).  The arrays
+ * are borrowed for the duration of the call. */
+dfgpu_status dfgpu_agg_push_arrow_batches(dfgpu_agg *agg, const struct ArrowArray *const *batches, int32_t n);
 dfgpu_status dfgpu_agg_num_groups(dfgpu_agg *agg, int64_t *out);
 /* Sharded aggregation, fused: AggregateExec(Partial) -> RepartitionExec(Hash(group keys), world) ->
  * AggregateExec(FinalPartitioned) (core/src/physical_planner.rs:814-849) collapsed into ONE operator per

@@ -169,6 +169,13 @@ impl GpuAgg {
         let (array, _schema) = export_batch(batch)?;
         check(unsafe { dfgpu_agg_push_arrow(self.ptr, &array) })
     }
+    /// Several batches the input stream had ready, in one call: the library packs them into its pinned arena with
+    /// several host threads (`dfgpu_agg_push_arrow_batches`).
+    pub fn push_many(&self, batches: &[RecordBatch]) -> Result<()> {
+        let exported = batches.iter().map(export_batch).collect::<Result<Vec<_>>>()?;
+        let ptrs: Vec<*const FFI_ArrowArray> = exported.iter().map(|(a, _)| a as *const FFI_ArrowArray).collect();
+        check(unsafe { dfgpu_agg_push_arrow_batches(self.ptr, ptrs.as_ptr(), ptrs.len() as i32) })
+    }
     pub fn exchange(&self) -> Result<()> {
         check(unsafe { dfgpu_agg_exchange(self.ptr) })
     }

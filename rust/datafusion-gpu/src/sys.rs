@@ -212,6 +212,7 @@ extern "C" {
     pub fn dfgpu_agg_output_schema(agg: *const dfgpu_agg, out_schema: *mut FFI_ArrowSchema) -> c_int;
     pub fn dfgpu_agg_push(agg: *mut dfgpu_agg, batch: *const dfgpu_batch) -> c_int;
     pub fn dfgpu_agg_push_arrow(agg: *mut dfgpu_agg, batch: *const FFI_ArrowArray) -> c_int;
+    pub fn dfgpu_agg_push_arrow_batches(agg: *mut dfgpu_agg, batches: *const *const FFI_ArrowArray, n: i32) -> c_int;
     pub fn dfgpu_agg_num_groups(agg: *mut dfgpu_agg, out: *mut i64) -> c_int;
     pub fn dfgpu_agg_exchange(agg: *mut dfgpu_agg) -> c_int;
     pub fn dfgpu_agg_exchange_virtual(aggs: *const *mut dfgpu_agg, n: i32) -> c_int;

@@ -408,6 +408,50 @@ def test_host_batch_coalescing(keys, target):
     ctx.close()
 
 
+@pytest.mark.parametrize("nulls", [0.0, 0.1], ids=["no_nulls_threaded_copy", "nulls_serial_copy"])
+@pytest.mark.parametrize("target", [4096, 1 << 20, -1], ids=["coalesce4096", "default", "off"])
+def test_push_many_equals_push(target, nulls):
+    """dfgpu_agg_push_arrow_batches: n host batches in one call give what n pushes give - runs of small batches are packed
+    into the arena together (several host threads when all columns are fixed-width and free of nulls), batches large enough
+    to bypass the arena and empty batches in between keep their place in the order."""
+    import datafusion_upstream_b200 as df
+    ctx = gpu_ctx(coalesce_rows=target)
+    rng = np.random.default_rng(4242 + int(nulls * 10))
+    n = 300_000
+    k = rng.integers(0, 5000, n)
+    v = rng.integers(-1000, 1000, n)
+    whole = pa.record_batch([pa.array(k, pa.int64(), mask=(rng.random(n) < nulls) if nulls else None), pa.array(v, pa.int32(), mask=(rng.random(n) < nulls) if nulls else None),
+                             pa.array(rng.random(n), pa.float64())], names=["k", "v", "f"])
+    lens = [8192] * 12 + [0, 100_000, 1, 8192, 77] + [8192] * 30
+    pieces, off = [], 0
+    for ln in lens:
+        ln = min(ln, n - off)
+        pieces.append(whole.slice(off, ln))
+        off += ln
+    if off < n:
+        pieces.append(whole.slice(off))
+    exprs = [df.AggregateExpr(df.AggFunc.Count, None, "c"), df.AggregateExpr(df.AggFunc.Sum, "v", "s"), df.AggregateExpr(df.AggFunc.Max, "f", "m"),
+             df.AggregateExpr(df.AggFunc.Count, "v", "cv")]
+    outs = []
+    for many in (False, True):
+        op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, whole.schema, ["k"], exprs)
+        if many:
+            op.push_many(pieces[:20])
+            op.push_many(pieces[20:])
+            op.push_many([])
+        else:
+            for p in pieces:
+                op.push(p)
+        outs.append(op.emit())
+        m = op.metrics()
+        assert m["input_rows"] == n and m["input_batches"] == len(pieces), m
+        op.close()
+    assert_tables_equal(outs[1], outs[0], key_cols=[0], what="push_many vs push")
+    want = oracle_agg("single", [whole], ["k"], [("count", None, "c", None), ("sum", "v", "s", None), ("max", "f", "m", None), ("count", "v", "cv", None)])
+    assert_tables_equal(outs[1], want, key_cols=[0], what="push_many vs oracle")
+    ctx.close()
+
+
 PA_T = {"int32": pa.int32(), "uint32": pa.uint32(), "int64": pa.int64(), "uint64": pa.uint64(), "float32": pa.float32(),
         "float64": pa.float64()}
 
