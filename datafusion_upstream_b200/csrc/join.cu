@@ -10,6 +10,7 @@
 //            into the count/scatter, then build_batch_from_indices (utils.rs:1180-1230) = take.
 //   final  : process_unmatched_build_batch / get_final_indices_from_bit_map
 //            (hash_join.rs:1348-1388, utils.rs:1119-1141) from the visited flags.
+#include <set>
 #include <chrono>
 
 #include "device.cuh"
@@ -250,44 +251,66 @@ static JKeys key_plan(const JoinOp &j, const std::vector<ColRef> &keys) {
     return jk;
 }
 
-// direct build of the probe index from the build rows (join_fast.inc)
-static void build_index(JoinOp &j) {
+// direct build of the probe index from the build rows (join_fast.inc): partition by table block, one CTA per block.
+// false: a block overflowed (keys that collide on the index hash) - the caller builds the general path instead.
+static bool build_index(JoinOp &j) {
     Ctx *ctx = j.ctx;
     cudaStream_t st = ctx->stream;
     const int64_t nb = j.build_rows;
-    j.jgroups = std::max<uint64_t>(4, ((uint64_t)nb * 2 + JG - 1) / JG);  // load factor <= 1/2
+    const uint64_t want = std::max<uint64_t>(4, ((uint64_t)nb * 2 + JG - 1) / JG);  // load factor <= 1/2
+    j.jgroups = (want + JB_G - 1) / JB_G * JB_G;
+    const uint32_t nblocks = (uint32_t)(j.jgroups / JB_G), nbins = nblocks + 2;
     const uint64_t nslots = j.jgroups * JG + 2;
     j.jtags = make_buf(ctx, j.jgroups * JG + 16);
     j.jslots = make_buf(ctx, nslots * 16 + 16);
-    BufRef bslot = make_buf(ctx, (size_t)nb * 4 + 16);
-    DevBuf flags(ctx, 16, true);  // [0] = some key repeats, [2..3] = rows[] cursor
-    DF_CUDA(cudaMemsetAsync(j.jtags->ptr, 0, j.jgroups * JG, st));
-    k_jb_init<<<grid_for((int64_t)nslots, 256, ctx, 8), 256, 0, st>>>(j.jslots->as<ulonglong2>(), nslots);
+    j.rows = make_buf(ctx, (size_t)nb * 4 + 16);
+    BufRef hist = make_buf(ctx, (size_t)nbins * 4 + 16, true), offs = make_buf(ctx, (size_t)(nbins + 1) * 4 + 16), cursors = make_buf(ctx, (size_t)nbins * 4 + 16);
+    BufRef recs = make_buf(ctx, (size_t)nb * 16 + 16);
+    DevBuf flags(ctx, 16, true);  // [0] = some key repeats, [1] = a block overflowed, [2..3] = rows[] cursor
+    {
+        static std::mutex mu;
+        static std::set<int> done;
+        std::lock_guard<std::mutex> lock(mu);
+        if (done.insert(ctx->device).second) DF_CUDA(cudaFuncSetAttribute(k_jbp_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jbp_build_smem()));
+    }
     std::vector<ColRef> keys = key_columns(ctx, *j.build, j.bkeys);
     JKeys jk = key_plan(j, keys);
-    const unsigned nt = (unsigned)((nb + JP_TILE - 1) / JP_TILE);
+    const int64_t ntiles = (nb + JP_TILE - 1) / JP_TILE;
+    const bool sm = nbins <= JB_SMEM_BINS;   // the bins fit shared memory: per-CTA counts, one global atomic per CTA and bin
+    const unsigned nt = (unsigned)std::min<int64_t>(ntiles, sm ? (int64_t)ctx->sm_count * 4 : ntiles);
+    const size_t smem = sm ? (size_t)nbins * 4 : 0;
+    BufRef cta_cnt = make_buf(ctx, sm ? (size_t)nt * nbins * 4 + 16 : 16);
     {
-        KTimer kt(ctx, "k_jb_insert", nb * 8);
-        if (jk.direct)
-            k_jb_insert<true><<<nt, JP_T, 0, st>>>(jk, nb, (uint32_t)j.jgroups, j.jtags->as<uint32_t>(), j.jslots->as<ulonglong2>(), bslot->as<uint32_t>(),
-                                                   flags.as<uint32_t>());
-        else
-            k_jb_insert<false><<<nt, JP_T, 0, st>>>(jk, nb, (uint32_t)j.jgroups, j.jtags->as<uint32_t>(), j.jslots->as<ulonglong2>(), bslot->as<uint32_t>(),
-                                                    flags.as<uint32_t>());
+        KTimer kt(ctx, "k_jb_partition", nb * 8);
+        uint32_t *h = hist->as<uint32_t>(), *cc = cta_cnt->as<uint32_t>(), *of = offs->as<uint32_t>(), *cu = cursors->as<uint32_t>();
+        const uint32_t ng = (uint32_t)j.jgroups;
+        if (jk.direct && sm) k_jbp_hist<true, true><<<nt, JP_T, smem, st>>>(jk, nb, ng, nbins, h, cc);
+        else if (jk.direct) k_jbp_hist<true, false><<<nt, JP_T, 0, st>>>(jk, nb, ng, nbins, h, cc);
+        else if (sm) k_jbp_hist<false, true><<<nt, JP_T, smem, st>>>(jk, nb, ng, nbins, h, cc);
+        else k_jbp_hist<false, false><<<nt, JP_T, 0, st>>>(jk, nb, ng, nbins, h, cc);
+        k_jbp_scan<<<1, 1024, 0, st>>>(h, nbins, of, cu);
+        if (jk.direct && sm) k_jbp_scatter<true, true><<<nt, JP_T, smem, st>>>(jk, nb, ng, nbins, of, cu, cc, recs->as<ulonglong2>());
+        else if (jk.direct) k_jbp_scatter<true, false><<<nt, JP_T, 0, st>>>(jk, nb, ng, nbins, of, cu, cc, recs->as<ulonglong2>());
+        else if (sm) k_jbp_scatter<false, true><<<nt, JP_T, smem, st>>>(jk, nb, ng, nbins, of, cu, cc, recs->as<ulonglong2>());
+        else k_jbp_scatter<false, false><<<nt, JP_T, 0, st>>>(jk, nb, ng, nbins, of, cu, cc, recs->as<ulonglong2>());
     }
-    note_launch(ctx, 2);
-    uint32_t dups = 0;
-    DF_CUDA(cudaMemcpyAsync(&dups, flags.ptr, 4, cudaMemcpyDeviceToHost, st));
+    {
+        KTimer kt(ctx, "k_jb_build", nb * 16);
+        k_jbp_build<<<nbins, JB_T, jbp_build_smem(), st>>>(recs->as<ulonglong2>(), offs->as<uint32_t>(), (uint32_t)j.jgroups, j.jtags->as<uint32_t>(), j.jslots->as<ulonglong2>(),
+                                                          j.rows->as<uint32_t>(), flags.as<uint32_t>());
+    }
+    note_launch(ctx, 4);
+    uint32_t hf[2] = {0, 0};
+    DF_CUDA(cudaMemcpyAsync(hf, flags.ptr, 8, cudaMemcpyDeviceToHost, st));
     DF_CUDA(cudaStreamSynchronize(st));
-    j.rows = make_buf(ctx, (dups ? (size_t)nb * 4 : 0) + 16);
-    if (dups) {
-        BufRef fill = make_buf(ctx, nslots * 4 + 16, true);
-        k_jb_starts<<<grid_for((int64_t)nslots, 256, ctx, 8), 256, 0, st>>>(j.jslots->as<ulonglong2>(), nslots, flags.as<unsigned long long>() + 1);
-        k_jb_fill<<<grid_for(nb, 256, ctx, 16), 256, 0, st>>>(j.jslots->as<ulonglong2>(), bslot->as<uint32_t>(), nb, fill->as<uint32_t>(),
-                                                             j.rows->as<uint32_t>());
-        note_launch(ctx, 2);
-    }
     DF_CUDA(cudaGetLastError());
+    if (hf[1]) {
+        j.jtags.reset();
+        j.jslots.reset();
+        j.rows.reset();
+        return false;
+    }
+    return true;
 }
 
 // fused probe: returns the (build_idx, probe_idx) pairs and their number
@@ -350,9 +373,8 @@ void join_build_finish(JoinOp &j) {
     int64_t nb = j.build->num_rows;
     if (nb >= (1LL << 32) - 1) fail(DFGPU_RESOURCES_EXHAUSTED, "Resources exhausted: build side larger than 2^32 rows");
     j.build_rows = nb;
-    j.fast = nb > 0 && fast_eligible(j, nb);
+    j.fast = nb > 0 && fast_eligible(j, nb) && build_index(j);
     if (j.fast) {
-        build_index(j);
         j.num_keys = 1;
     } else if (nb) {
         BufRef gids = make_buf(ctx, (size_t)nb * 4 + 16);
