@@ -1028,19 +1028,20 @@ struct TakeCol {
     const uint8_t *src;
     uint8_t *dst;
     const int64_t *idx;
-    int32_t w, pad;
+    int32_t w, stride;   // element j of the source lies at src + stride * j (a plain column: stride = w; a field of packed rows: the row size)
 };
 struct TakePlan {
     TakeCol c[TAKE_MAXCOLS];
     int32_t n, pad;
 };
-DF_D uint4 take_load(const uint8_t *src, int w, int64_t j) {
+DF_D uint4 take_load(const uint8_t *src, int w, int64_t j, int stride) {
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (w == 16) v = *(const uint4 *)(src + 16 * j);
-    else if (w == 8) { const uint2 t = *(const uint2 *)(src + 8 * j); v.x = t.x; v.y = t.y; }
-    else if (w == 4) v.x = *(const uint32_t *)(src + 4 * j);
-    else if (w == 2) v.x = *(const uint16_t *)(src + 2 * j);
-    else v.x = src[j];
+    src += (int64_t)stride * j;
+    if (w == 16) v = *(const uint4 *)src;
+    else if (w == 8) { const uint2 t = *(const uint2 *)src; v.x = t.x; v.y = t.y; }
+    else if (w == 4) v.x = *(const uint32_t *)src;
+    else if (w == 2) v.x = *(const uint16_t *)src;
+    else v.x = *src;
     return v;
 }
 DF_D void take_store(uint8_t *dst, int w, int64_t i, const uint4 &v) {
@@ -1050,6 +1051,15 @@ DF_D void take_store(uint8_t *dst, int w, int64_t i, const uint4 &v) {
     else if (w == 2) *(uint16_t *)(dst + 2 * i) = (uint16_t)v.x;
     else dst[i] = (uint8_t)v.x;
 }
+// columns -> packed rows: TakeCol.src = the column, .dst = the field's place in row 0, .stride = the row size
+__global__ void __launch_bounds__(256) k_pack_rows(const __grid_constant__ TakePlan p, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        for (int c = 0; c < p.n; c++) {
+            const uint4 v = take_load(p.c[c].src, p.c[c].w, i, p.c[c].w);
+            take_store(p.c[c].dst + (int64_t)p.c[c].stride * i, p.c[c].w, 0, v);
+        }
+}
 __global__ void __launch_bounds__(256) k_take_multi(const __grid_constant__ TakePlan p, int64_t n) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -1057,7 +1067,7 @@ __global__ void __launch_bounds__(256) k_take_multi(const __grid_constant__ Take
             uint4 v[4];
 #pragma unroll
             for (int q = 0; q < 4; q++)
-                if (c0 + q < p.n) v[q] = take_load(p.c[c0 + q].src, p.c[c0 + q].w, p.c[c0 + q].idx[i]);
+                if (c0 + q < p.n) v[q] = take_load(p.c[c0 + q].src, p.c[c0 + q].w, p.c[c0 + q].idx[i], p.c[c0 + q].stride);
 #pragma unroll
             for (int q = 0; q < 4; q++)
                 if (c0 + q < p.n) take_store(p.c[c0 + q].dst, p.c[c0 + q].w, i, v[q]);
@@ -1065,8 +1075,42 @@ __global__ void __launch_bounds__(256) k_take_multi(const __grid_constant__ Take
     }
 }
 
+// Fixed-width columns without nulls packed row-wise: a gather of several of them by the same index then costs one DRAM line
+// per row instead of one per column (a random 8-byte load pulls a whole 128-byte line on this part: ncu measured 117 B of
+// DRAM read per gathered value).  Fields sit at offsets aligned to their width; rows are padded to 16 / 32 / 64 bytes so
+// that no row straddles a line.  Returns an empty PackedRows when fewer than two columns qualify or a row would exceed 64 bytes.
+PackedRows pack_rows(Ctx *ctx, const std::vector<ColRef> &cols, int64_t n) {
+    PackedRows pr;
+    pr.off.assign(cols.size(), -1);
+    std::vector<int> take;
+    for (int w : {16, 8, 4, 2, 1})   // widest first: every field is aligned to its width
+        for (size_t c = 0; c < cols.size(); c++) {
+            const DevCol &src = *cols[c];
+            if (src.type.id == T_DICT || src.type.id == T_BOOL || type_width(src.type.id) != w || (src.validity && src.null_count != 0)) continue;
+            take.push_back((int)c);
+        }
+    int bytes = 0;
+    for (int c : take) bytes += type_width(cols[(size_t)c]->type.id);
+    if (take.size() < 2 || bytes > 64 || n == 0 || (int)take.size() > TAKE_MAXCOLS) return pr;
+    pr.row_bytes = bytes <= 16 ? 16 : bytes <= 32 ? 32 : 64;
+    pr.rows = make_buf(ctx, (size_t)n * pr.row_bytes + 16);
+    TakePlan p;
+    memset(&p, 0, sizeof p);
+    int at = 0;
+    for (int c : take) {
+        const int w = type_width(cols[(size_t)c]->type.id);
+        pr.off[(size_t)c] = at;
+        p.c[p.n++] = TakeCol{(const uint8_t *)cols[(size_t)c]->values, pr.rows->as<uint8_t>() + at, nullptr, w, pr.row_bytes};
+        at += w;
+    }
+    k_pack_rows<<<grid_for(n, 256, ctx, 16), 256, 0, ctx->stream>>>(p, n);
+    note_launch(ctx);
+    DF_CUDA(cudaGetLastError());
+    return pr;
+}
+
 std::vector<ColRef> cols_take(Ctx *ctx, const std::vector<const DevCol *> &srcs, const std::vector<const int64_t *> &idx, int64_t n,
-                              const std::vector<bool> &idx_may_be_null) {
+                              const std::vector<bool> &idx_may_be_null, const std::vector<std::pair<const uint8_t *, int>> *packed) {
     std::vector<ColRef> out(srcs.size());
     TakePlan p;
     memset(&p, 0, sizeof p);
@@ -1092,7 +1136,8 @@ std::vector<ColRef> cols_take(Ctx *ctx, const std::vector<const DevCol *> &srcs,
         c->owned.push_back(b);
         c->values = b->ptr;
         c->dict = src.dict;
-        p.c[p.n++] = TakeCol{(const uint8_t *)src.values, b->as<uint8_t>(), idx[k], w, 0};
+        if (packed && (*packed)[k].first) p.c[p.n++] = TakeCol{(*packed)[k].first, b->as<uint8_t>(), idx[k], w, (*packed)[k].second};
+        else p.c[p.n++] = TakeCol{(const uint8_t *)src.values, b->as<uint8_t>(), idx[k], w, w};
         out[k] = c;
         if (p.n == TAKE_MAXCOLS) flush();
     }

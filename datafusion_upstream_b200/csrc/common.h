@@ -363,8 +363,15 @@ Batch *batch_eval_decimal(Ctx *ctx, const Batch *b, const dfgpu_expr_node *nodes
 // gather rows (compute::take); idx < 0 => NULL row.  idx is a device array of n int64.
 ColRef col_take(Ctx *ctx, const DevCol &src, const int64_t *idx, int64_t n, bool idx_may_be_null);
 // the same for several columns (each with its own index array): plain fixed-width columns share one launch
+// packed: per column an alternative source (first != nullptr): the column's field inside row-wise packed rows and the row size
 std::vector<ColRef> cols_take(Ctx *ctx, const std::vector<const DevCol *> &srcs, const std::vector<const int64_t *> &idx, int64_t n,
-                              const std::vector<bool> &idx_may_be_null);
+                              const std::vector<bool> &idx_may_be_null, const std::vector<std::pair<const uint8_t *, int>> *packed = nullptr);
+struct PackedRows {
+    BufRef rows;            // [n][row_bytes], empty when packing does not apply
+    int row_bytes = 0;
+    std::vector<int> off;   // per input column: offset of its field in a row, -1 = not packed
+};
+PackedRows pack_rows(Ctx *ctx, const std::vector<ColRef> &cols, int64_t n);
 ColRef col_nulls(Ctx *ctx, const TypeInfo &t, int64_t n);
 ColRef col_decode_dictionary(Ctx *ctx, const DevCol &src);  // Dictionary -> plain value type
 int64_t count_nulls(Ctx *ctx, const uint8_t *validity, int64_t vbit, int64_t n);

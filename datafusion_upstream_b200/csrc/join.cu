@@ -28,6 +28,7 @@ struct dfgpu_join {
     std::unique_ptr<dfgpu::GroupTable> table;
     dfgpu::BufRef span, rows, visited, gid_scratch;
     dfgpu::BufRef jtags, jslots;  // probe-side index of the fused path (join_fast.inc)
+    dfgpu::PackedRows brows;      // the build side's plain columns row-wise: one DRAM line per matched build row when the output is gathered
     uint64_t jgroups = 0;
     bool fast = false;
     int64_t build_rows = 0, num_keys = 0;
@@ -400,9 +401,15 @@ void join_build_finish(JoinOp &j) {
         DF_CUDA(cudaGetLastError());
     }
     if (need_final(j.join_type)) j.visited = make_buf(ctx, (size_t)nb + 16, true);
+    // build columns that reach the output: row-wise copy for the gathers of the probe phase (not worth it for tiny build sides,
+    // which stay in L2, nor for joins that never emit build columns)
+    const int jt0 = j.join_type;
+    if (nb >= (1 << 20) && jt0 != DFGPU_JOIN_RIGHT_SEMI && jt0 != DFGPU_JOIN_RIGHT_ANTI && jt0 != DFGPU_JOIN_LEFT_SEMI && jt0 != DFGPU_JOIN_LEFT_ANTI &&
+        jt0 != DFGPU_JOIN_RIGHT && jt0 != DFGPU_JOIN_FULL)
+        j.brows = pack_rows(ctx, j.build->cols, nb);
     j.finished = true;
     j.m.build_mem_used = (int64_t)(j.table->device_bytes() + (j.span ? j.span->bytes : 0) + (j.rows ? j.rows->bytes : 0) +
-                                   (j.jslots ? j.jslots->bytes + j.jtags->bytes : 0));
+                                   (j.jslots ? j.jslots->bytes + j.jtags->bytes : 0) + (j.brows.rows ? j.brows.rows->bytes : 0));
     DF_CUDA(cudaStreamSynchronize(st));
     j.m.build_time_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
 }
@@ -475,18 +482,22 @@ static Batch *materialize(JoinOp &j, const std::vector<ColRef> &probe_cols, cons
     std::vector<const DevCol *> srcs;
     std::vector<const int64_t *> idx;
     std::vector<bool> may_null;
+    std::vector<std::pair<const uint8_t *, int>> packed;
     if (left_out && j.build_rows != 0)
-        for (auto &c : j.build->cols) {
-            srcs.push_back(c.get());
+        for (size_t c = 0; c < j.build->cols.size(); c++) {
+            srcs.push_back(j.build->cols[c].get());
             idx.push_back(ob->as<int64_t>());
             may_null.push_back(build_nullable);
+            const bool pk = j.brows.rows && j.brows.off[c] >= 0;
+            packed.emplace_back(pk ? j.brows.rows->as<uint8_t>() + j.brows.off[c] : nullptr, j.brows.row_bytes);
         }
     for (auto &c : probe_cols) {
         srcs.push_back(c.get());
         idx.push_back(op->as<int64_t>());
         may_null.push_back(false);
+        packed.emplace_back(nullptr, 0);
     }
-    for (auto &t : cols_take(ctx, srcs, idx, total, may_null)) {
+    for (auto &t : cols_take(ctx, srcs, idx, total, may_null, &packed)) {
         t->type = j.out_schema.fields[fi++];
         out->cols.push_back(t);
     }

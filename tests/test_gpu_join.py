@@ -177,6 +177,34 @@ def test_join_q3_shape_large(ctx):
     assert_rows_equal(rows_of(got), rows_of(want))
 
 
+@pytest.mark.parametrize("jt", ["inner", "left", "full"])
+def test_join_large_build_packed_rows_and_block_build(ctx, jt):
+    """A build side of > 2^20 rows: the index is built block by block from partitioned rows (more blocks than one CTA histogram
+    holds in the Partitioned variant below is covered by bench sizes), keys that repeat get their runs in rows[], and the build
+    columns that reach the output are gathered from row-wise packed rows (Inner / Left; Full keeps the column-wise gather because
+    unmatched probe rows carry NULL build columns) - mixed widths, one nullable and one string column that stay column-wise."""
+    rng = np.random.default_rng(11)
+    nb, np_ = 1_200_000, 120_000
+    bk = rng.integers(0, 900_000, nb).astype(np.int64)          # ~ 25 % of the keys repeat
+    bk[:5] = [-1, -1, 2**63 - 1, -2**63, 7]
+    build = pa.record_batch([
+        pa.array(bk),
+        pa.array(rng.integers(-2**31, 2**31, nb), pa.int32()),
+        pa.array(rng.integers(0, 2**15, nb), pa.int16()),
+        pa.array(rng.random(nb), pa.float64()),
+        pa.array(rng.integers(-10**9, 10**9, nb), pa.int64()).cast(pa.decimal128(25, 2)),
+        pa.array(rng.integers(0, 100, nb), pa.int64(), mask=rng.random(nb) < 0.05),
+        pa.array([f"s{v}" for v in rng.integers(0, 1000, nb)]),
+        pa.array(rng.integers(0, 255, nb), pa.uint8()),
+    ], names=["k", "i32", "i16", "f64", "dec", "nullable", "str", "u8"])
+    pk = rng.integers(-100_000, 1_000_000, np_).astype(np.int64)
+    pk[:3] = [-1, 2**63 - 1, 12345678901]
+    probe = pa.record_batch([pa.array(pk), pa.array(np.arange(np_), pa.int64())], names=["pk", "y"])
+    out, _ = gpu_join(ctx, jt, [build.slice(0, 500_000), build.slice(500_000)], [probe.slice(0, 150_000), probe.slice(150_000)], [(0, 0)])
+    want = oracle.hash_join(jt, [build], [probe], [(0, 0)])
+    assert_rows_equal(rows_of(out), rows_of(want), what=jt)
+
+
 @pytest.mark.parametrize("jt", ALL_TYPES)
 @pytest.mark.parametrize("n_probe", [1, 1023, 1024, 1025, 2047, 2048, 2049, 3 * 2048 + 5])
 def test_join_index_edges(ctx, jt, n_probe):
