@@ -114,6 +114,8 @@ class FastAgg {
     size_t device_bytes() const;
     // what the sample of the first push said (tests, metrics): 1 cache path, 2 partition path, 0 not decided yet
     int path_mode() const { return mode_; }
+    bool count_only_op() const { return count_only(); }
+    size_t record_bytes() const { return (size_t)RW_ * 8; }
 
   private:
     void ensure_capacity(int64_t more);
