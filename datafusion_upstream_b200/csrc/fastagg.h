@@ -58,6 +58,7 @@ struct FaRegPlan {
     uint32_t seen[FA_MAXROLES];   // seen bits of every logical op computed by accumulator i
     int32_t woff[FA_MAXROLES];    // word offset in the CTA's partial record
     int32_t alias[FA_MAX_OPS];    // logical op -> word offset of the accumulator that computes it
+    int32_t general_keys, pad;    // test / A-B hook (DFGPU_FA_NOK8=1): key phase without the one-byte-key form
 };
 
 // pieces of a partition's records after the record exchange between ranks (level 2 input)
