@@ -132,6 +132,8 @@ class FastAgg {
     struct Xchg;
     bool count_only() const { return ops_.size() == 1 && ops_[0].kind == 1 /* OP_COUNT */ && nbits_ == 0 && SW_ == 1; }
     size_t xchg_meta_bytes() const;
+    size_t xchg_small_off() const;
+    void xchg_finish_small(Xchg &x, const BufRef &meta_all_dev);   // every rank's records rode in the meta blocks: keep the owned ones
     void xchg_prepare(Xchg &x, int W, int me);                                      // local: partition order, meta block on the device
     size_t xchg_plan(Xchg &x, const std::vector<uint8_t> &meta_all);                // from everybody's meta: what goes where; bytes my window needs
     void xchg_push(Xchg &x, void *const *windows);                                  // my runs -> the owners' windows
@@ -141,6 +143,7 @@ class FastAgg {
     void xchg_finish_pull(Xchg &x, const uint64_t *const *src, const int64_t *recv, const BufRef &meta_all_dev);
     BufRef arena_buf(size_t bytes, int64_t *arena_off);   // from the send arena when this operator may use it, else from the pool
     void arena_refresh();                                 // the arena moved: re-derive the pieces' pointers
+    bool remote_loop_ = false;    // DFGPU_FA_REMOTE_LOOP=1
     bool xpull_ = false;          // the exchange that ran was a pull between real ranks: finalize ends with the closing barrier
     std::vector<BufRef> xhold_;        // received window (virtual ranks), gathered meta, piece tables: alive until the merge ran
     BufRef xp_offs_, xp_hist_;         // [npieces][FA_P] of the received pieces (count-only operators)

@@ -164,6 +164,42 @@ def test_register_mode_q1_shape_and_late_keys(ctx):
     assert_tables_equal(got, want, key_cols=[0, 1])
 
 
+@pytest.mark.parametrize("general", ["0", "1"], ids=["one_byte_key_form", "general_key_phase"])
+@pytest.mark.parametrize("shape", ["u8_u8", "u8", "utf8_utf8", "sliced_unaligned"])
+def test_register_mode_one_byte_keys(ctx, monkeypatch, shape, general):
+    """Register mode maps one-byte key columns to groups four rows at a time (one 32-bit load per column, 16-bit codes): row
+    counts that are not a multiple of four, groups that first appear late (claimed from inside a quad), a slice whose key
+    buffers are not 4-byte aligned (takes the general form), one and two key columns, one-byte strings read in place."""
+    monkeypatch.setenv("DFGPU_FA_NOK8", general)
+    rng = np.random.default_rng(31)
+    n = 262_147
+    pick = rng.choice(4, n, p=[0.25, 0.006, 0.493, 0.251])
+    f = np.array([65, 78, 78, 82], np.uint8)[pick]
+    st = np.array([70, 70, 79, 70], np.uint8)[pick]
+    f[200_001:200_007] = 90                 # a 5th group long after the probe sample: slow rows
+    f[-1] = 66
+    v = pa.array(rng.integers(-10**6, 10**6, n), pa.int64())
+    if shape == "utf8_utf8":
+        keys = [pa.array([chr(c) for c in f]), pa.array([chr(c) for c in st])]
+    else:
+        keys = [pa.array(f), pa.array(st)]
+    if shape == "u8":
+        b = pa.record_batch([keys[0], v], names=["f", "v"])
+        gk = ["f"]
+    else:
+        b = pa.record_batch(keys + [v], names=["f", "s", "v"])
+        gk = ["f", "s"]
+    if shape == "sliced_unaligned":
+        b = b.slice(1)
+    specs = [("count", None, "c", None), ("sum", "v", "sv", None), ("avg", "v", "av", None), ("min", "v", "mn", None)]
+    ctx.set_profiling(True)
+    got = gpu_agg(ctx, "single", [b], gk, specs)
+    names = {x["name"] for x in ctx.profile()}
+    ctx.set_profiling(False)
+    assert "k_fa_l1_reg" in names, names
+    assert_tables_equal(got, oracle_agg("single", [b], gk, specs), key_cols=list(range(len(gk))))
+
+
 def test_num_groups_mid_stream_then_more_input(ctx):
     """num_groups() compacts the record store; the operator keeps accepting input afterwards."""
     import datafusion_upstream_b200 as df

@@ -81,7 +81,7 @@ def test_general_accumulators_over_record_pieces(monkeypatch, world, hook):
         ctx.close()
 
 
-@pytest.mark.parametrize("model", ["pull", "push"])
+@pytest.mark.parametrize("model", ["pull", "pull_remote_loop", "push"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("modes", ["all_partition", "all_cache", "mixed"])
 def test_count_star_key_and_record_pieces(monkeypatch, world, modes, model):
@@ -90,7 +90,9 @@ def test_count_star_key_and_record_pieces(monkeypatch, world, modes, model):
     other ranks' streams where they lie (the default between real ranks: NVLink loads); push: runs are copied into the owner's
     window first (the fallback, and the path of operators with other accumulators)."""
     import datafusion_upstream_b200 as df
-    monkeypatch.setenv("DFGPU_EXCHANGE", model)
+    monkeypatch.setenv("DFGPU_EXCHANGE", "push" if model == "push" else "pull")
+    if model == "pull_remote_loop":   # the merge loop that real ranks use for pieces in another GPU's memory (4 keys per lane in flight, no prefetch)
+        monkeypatch.setenv("DFGPU_FA_REMOTE_LOOP", "1")
     ctx = gpu_ctx()
     try:
         rng = np.random.default_rng(100 + world)
@@ -122,6 +124,33 @@ def test_count_star_key_and_record_pieces(monkeypatch, world, modes, model):
         check_union(outs, shards, ["k"], COUNT, 1)
         null_rows = [i for i, o in enumerate(outs) if o.num_rows and o.column(0).null_count]
         assert null_rows == [0]
+    finally:
+        ctx.close()
+
+
+@pytest.mark.parametrize("groups", [4, 200, 300], ids=["q1_like_4_groups", "200_groups", "300_groups_regular_path"])
+@pytest.mark.parametrize("world", [2, 5, 8])
+def test_small_states_ride_in_the_meta_blocks(world, groups):
+    """Ranks whose partial states compact to <= 256 records put them into their meta block; when every rank did, the all-gather
+    was the exchange (no window, push, barrier or plan).  One rank is empty, one holds NULL keys (side group -> rank 0); with 300
+    groups per rank the regular path runs instead, after the same compaction."""
+    ctx = gpu_ctx()
+    try:
+        rng = np.random.default_rng(world * 1000 + groups)
+        shards = []
+        for r in range(world):
+            n = 0 if r == 1 else 5_000 + 100 * r
+            k = rng.integers(0, groups, n).astype(np.int64) * 7919 - 3
+            b = pa.record_batch([pa.array(k, pa.int64(), mask=(rng.random(n) < 0.01) if r == 0 else None), random_values(rng, n, "int64", 0.1),
+                                 random_values(rng, n, "decimal", 0.1), random_values(rng, n, "float64", 0.05)], names=["k", "v", "d", "f"])
+            shards.append([b])
+        names = set()
+        outs = run_virtual(ctx, shards, ["k"], MIXED, names)
+        assert ("stage:record_exchange_small" in names) == (groups <= 200), names
+        check_union(outs, shards, ["k"], MIXED, 1)
+        allk = [x for o in outs if o.num_rows for x in o.column(0).to_pylist()]
+        assert len(allk) == len(set(allk))
+        assert all(o.column(0).null_count == 0 for o in outs[1:] if o.num_rows)   # the NULL group comes out of rank 0
     finally:
         ctx.close()
 
