@@ -735,11 +735,16 @@ def run_agg(env, args, with_e2e=True, with_cpu=True):
                 exported.append((a, sc))
             L = N.lib()
 
+            ptrs = (ctypes.c_void_p * len(exported))(*[ctypes.addressof(a) for a, _ in exported])
+
             def e2e_step():
                 hold.clear()
                 op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, w["schema"], w["group_by"], w["exprs"])
-                for a, _ in exported:
-                    N.check(L.dfgpu_agg_push_arrow(op.h, ctypes.addressof(a)))
+                if args.batch_api == "many":      # what the stream has ready, in one call (packed by several host threads)
+                    N.check(L.dfgpu_agg_push_arrow_batches(op.h, ptrs, len(exported)))
+                else:
+                    for a, _ in exported:
+                        N.check(L.dfgpu_agg_push_arrow(op.h, ctypes.addressof(a)))
                 out = op.emit()
                 hold[:] = [(op, out)]
                 return out
@@ -749,6 +754,7 @@ def run_agg(env, args, with_e2e=True, with_cpu=True):
         if exported:
             e2e["batch_rows"] = args.batch_rows
             e2e["pushes_per_step"] = len(exported)
+            e2e["batch_api"] = "dfgpu_agg_push_arrow_batches" if args.batch_api == "many" else "dfgpu_agg_push_arrow"
             for a, sc in exported:
                 if a.release:
                     ctypes.CFUNCTYPE(None, ctypes.POINTER(N.ArrowArray))(a.release)(ctypes.byref(a))
@@ -1234,6 +1240,7 @@ def main():
     ap.add_argument("--targets-sf", type=int, default=100)
     ap.add_argument("--targets-steps", type=int, default=5)
     ap.add_argument("--batch-rows", type=int, default=0, help="e2e leg: push the host batch in slices of this many rows (8192 = the reference's batch_size)")
+    ap.add_argument("--batch-api", default="one", choices=["one", "many"], help="with --batch-rows: one dfgpu_agg_push_arrow per slice, or all slices in one dfgpu_agg_push_arrow_batches call")
     ap.add_argument("--q1-keys", default="u8", choices=["u8", "utf8"], help="q1: key columns as 2 x UInt8 (default) or 2 x Utf8 as in configs[0]")
     ap.add_argument("--q1-project", action="store_true", help="q1: compute disc_price / charge on the device from price, discount, tax")
     ap.add_argument("--chunk-rows", type=int, default=0, help="dfgpu_options.chunk_rows (rows per internal launch wave; 0 = default)")

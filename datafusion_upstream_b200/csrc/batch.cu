@@ -598,7 +598,7 @@ Batch *batch_import(Ctx *ctx, const ArrowArray *arr, const Schema &schema, bool 
         if (ch->length != arr->length) fail(DFGPU_INTERNAL, "column length mismatch in RecordBatch");
         b->cols.push_back(import_array(ctx, ch, schema.fields[(size_t)i], on_device));
     }
-    if (ctx->import_pinned_pending) {
+    if (ctx->import_pinned_pending && !ctx->import_defer_wait) {
         // the caller may release or reuse its (pinned) buffers as soon as this call returns: the copies must have read them
         ctx->import_pinned_pending = false;
         if (!ctx->import_event) DF_CUDA(cudaEventCreateWithFlags(&ctx->import_event, cudaEventDisableTiming));

@@ -73,6 +73,7 @@ void ctx_release(Ctx *c) {
     }
     ctx_destroy_nccl(c);
     if (c->import_event) cudaEventDestroy(c->import_event);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     cudaStreamDestroy(c->stream);
     delete c;
 }

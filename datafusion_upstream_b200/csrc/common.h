@@ -16,6 +16,8 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <functional>
+#include <condition_variable>
 #include <vector>
 
 #include "../../include/dfgpu.h"
@@ -146,6 +148,7 @@ struct dfgpu_ctx {
     unsigned long long *guard_words = nullptr;  // [0] = corrupted red zones seen, [1] = size of the first offender
     uint64_t *flush_dummy = nullptr;
     bool import_pinned_pending = false;   // batch_import queued a copy out of pinned host memory (batch.cu upload())
+    bool import_defer_wait = false;       // the caller of batch_import waits for those copies itself (pipelined push, agg_host.inc)
     cudaEvent_t import_event = nullptr;
     std::atomic<int> refs{1};  // the creator's handle + every batch / operator created on this ctx
     // optional per-kernel CUDA-event timing (bench.py roofline): name -> (events, launches)
@@ -340,6 +343,7 @@ class HostCoalescer {
     static bool supports(const Schema &schema);   // fixed-width, Boolean and Utf8/Binary columns; no dictionaries
     int64_t rows() const { return rows_; }
     int64_t target() const { return target_; }
+    void set_target(int64_t rows) { target_ = rows; }   // takes effect with the next append (the arenas grow on demand)
     int64_t flushes() const { return flushes_; }
     bool fits(const ArrowArray *batch) const;     // false: flush first (i32 offsets of a Utf8 column would overflow)
     void append(const ArrowArray *batch);         // copies; the caller may release the batch afterwards

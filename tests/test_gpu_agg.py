@@ -9,7 +9,7 @@ import numpy as np
 import pyarrow as pa
 import pytest
 
-from gpu_helpers import gpu_agg, gpu_ctx, oracle_agg, random_keys, random_values
+from gpu_helpers import FUNCS, gpu_agg, gpu_ctx, oracle_agg, random_keys, random_values
 from util import assert_rows_equal, assert_tables_equal, rows_of
 
 pytestmark = pytest.mark.gpu
@@ -450,6 +450,42 @@ def test_push_many_equals_push(target, nulls):
     want = oracle_agg("single", [whole], ["k"], [("count", None, "c", None), ("sum", "v", "s", None), ("max", "f", "m", None), ("count", "v", "cv", None)])
     assert_tables_equal(outs[1], want, key_cols=[0], what="push_many vs oracle")
     ctx.close()
+
+
+@pytest.mark.parametrize("shape", ["count_star_int64", "mixed_nullable", "q1_like"])
+def test_pipelined_host_push(monkeypatch, shape):
+    """A large host batch of fixed-width columns is copied chunk by chunk on a second stream while the kernels of the previous
+    chunk run (DFGPU_PIPELINED_PUSH lowers the size at which that starts): same result as one import + push, validity bitmaps
+    with bit offsets per chunk, metrics count one batch."""
+    import datafusion_upstream_b200 as df
+    monkeypatch.setenv("DFGPU_PIPELINED_PUSH", "50000")
+    rng = np.random.default_rng(99)
+    n = 333_337
+    if shape == "count_star_int64":
+        monkeypatch.setenv("DFGPU_FA_PART", "1")
+        b = pa.record_batch([pa.array(rng.integers(0, 90_000, n), pa.int64())], names=["k"])
+        gk, specs = ["k"], [("count", None, "c", None)]
+    elif shape == "mixed_nullable":
+        b = pa.record_batch([pa.array(rng.integers(0, 3000, n), pa.int32(), mask=rng.random(n) < 0.02), pa.array(rng.integers(-99, 99, n), pa.int64(), mask=rng.random(n) < 0.1),
+                             pa.array(rng.random(n), pa.float64())], names=["k", "v", "f"])
+        gk, specs = ["k"], [("count", None, "c", None), ("sum", "v", "s", None), ("avg", "f", "a", None), ("count", "v", "cv", None)]
+    else:
+        b = pa.record_batch([pa.array(rng.integers(65, 68, n).astype(np.uint8)), pa.array(rng.integers(70, 72, n).astype(np.uint8)),
+                             pa.array(rng.integers(0, 10**6, n), pa.int64()).cast(pa.decimal128(25, 2))], names=["f", "s", "d"])
+        gk, specs = ["f", "s"], [("sum", "d", "sd", None), ("avg", "d", "ad", None), ("count", None, "c", None)]
+    ctx = gpu_ctx()
+    try:
+        exprs = [df.AggregateExpr(df.AggFunc(FUNCS[f]), a_, nm, fl) for f, a_, nm, fl in specs]
+        op = df.GpuAggregateExec(ctx, df.AggregateMode.Single, b.schema, gk, exprs)
+        op.push(b.slice(3))            # (a slice: value and validity buffers start at an offset)
+        op.push(b.slice(0, 3))
+        got = op.emit()
+        m = op.metrics()
+        assert m["input_rows"] == n and m["input_batches"] == 2, m
+        op.close()
+        assert_tables_equal(got, oracle_agg("single", [b], gk, specs), key_cols=list(range(len(gk))), what=shape)
+    finally:
+        ctx.close()
 
 
 PA_T = {"int32": pa.int32(), "uint32": pa.uint32(), "int64": pa.int64(), "uint64": pa.uint64(), "float32": pa.float32(),
