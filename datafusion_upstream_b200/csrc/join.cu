@@ -278,7 +278,9 @@ static bool build_index(JoinOp &j) {
     JKeys jk = key_plan(j, keys);
     const int64_t ntiles = (nb + JP_TILE - 1) / JP_TILE;
     const bool sm = nbins <= JB_SMEM_BINS;   // the bins fit shared memory: per-CTA counts, one global atomic per CTA and bin
-    const unsigned nt = (unsigned)std::min<int64_t>(ntiles, sm ? (int64_t)ctx->sm_count * 4 : ntiles);
+    // (persistent CTAs: as many as shared memory lets an SM hold - the scatter is latency-bound, ncu: 5 % issue-slot use at 4 per SM)
+    const int per_sm = sm ? std::max(1, std::min(8, (int)(((size_t)200 << 10) / ((size_t)nbins * 4 + 1024)))) : 8;
+    const unsigned nt = (unsigned)std::min<int64_t>(ntiles, sm ? (int64_t)ctx->sm_count * per_sm : ntiles);
     const size_t smem = sm ? (size_t)nbins * 4 : 0;
     BufRef cta_cnt = make_buf(ctx, sm ? (size_t)nt * nbins * 4 + 16 : 16);
     {
