@@ -269,10 +269,20 @@ impl ExecutionPlan for GpuAggregateExec {
         let output_rows = MetricBuilder::new(&self.metrics).output_rows(partition);
         let schema_for_cast = out_schema.clone();
         let stream = futures::stream::once(async move {
-            // ReadingInput (row_hash.rs:423-470)
-            while let Some(b) = input.next().await {
-                let projected = evaluate_projection(&p, &b?)?;
-                agg.push(&projected)?;
+            // ReadingInput (row_hash.rs:423-470).  Whatever the child has ready is handed over in one ABI call
+            // (`ready_chunks` never waits for more than one batch): the library packs the run into its pinned arena
+            // with several host threads instead of one copy per call.
+            let mut input = input.ready_chunks(64);
+            while let Some(ready) = input.next().await {
+                let mut projected = Vec::with_capacity(ready.len());
+                for b in ready {
+                    projected.push(evaluate_projection(&p, &b?)?);
+                }
+                if projected.len() == 1 {
+                    agg.push(&projected[0])?;
+                } else {
+                    agg.push_many(&projected)?;
+                }
             }
             if fused {
                 agg.exchange()?; // collective: every rank of the context's communicator runs this plan
